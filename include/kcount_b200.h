@@ -1,0 +1,212 @@
+/*
+ * kcount_b200.h -- C ABI of the B200-native k-mer analysis ("kcount") stage.
+ *
+ * This is the drop-in boundary. Plain pointers and sizes only: no CUDA, torch
+ * or C++ types. Every call returns KC_OK (0) or a negative kc_status; the text of the last error of a
+ * context is available from kc_last_error(). Nothing in this library falls back to the CPU: without a
+ * CUDA device every compute entry point fails with KC_ERR_CUDA.
+ *
+ * Reference interfaces each group replaces (paths relative to the reference tree):
+ *   kc_create/kc_destroy     <- KmerDHT<MAX_K>::KmerDHT / ~KmerDHT                 src/kcount/kmer_dht.cpp:104-166
+ *                               + HashTableInserter<MAX_K>::init                    src/kcount/kcount_gpu.cpp:225-267
+ *                               + HashTableGPUDriver<MAX_K>::init                   src/kcount/kcount-gpu/gpu_hash_table.cpp:528-650
+ *   kc_add_reads             <- the read loop of count_kmers()                      src/kcount/kcount.cpp:71-90
+ *                               (input = PackedRead bytes, src/packed_reads.cpp:99-126)
+ *   kc_parse                 <- SeqBlockInserter<MAX_K>::process_seq/process_block  src/kcount/kcount_gpu.cpp:111-180
+ *                               + ParseAndPackGPUDriver::process_seq_block          src/kcount/kcount-gpu/parse_and_pack.cpp:281-338
+ *   kc_exchange_*            <- KmerDHT::add_supermer / flush_updates (UPC++ RPCs)  src/kcount/kmer_dht.cpp:248-258
+ *   kc_insert                <- HashTableInserter<MAX_K>::insert_supermer           src/kcount/kcount_gpu.cpp:288-292
+ *                               + HashTableGPUDriver::insert_supermer_block         src/kcount/kcount-gpu/gpu_hash_table.cpp:656-735
+ *   kc_finalize              <- HashTableInserter::insert_into_local_hashtable      src/kcount/kcount_gpu.cpp:372-506
+ *                               + HashTableGPUDriver::done_all_inserts              src/kcount/kcount-gpu/gpu_hash_table.cpp:737-785
+ *   kc_result_*              <- begin_iterate / get_next_entry                      src/kcount/kcount-gpu/gpu_hash_table.cpp:812-827
+ *                               + KmerDHT::local_kmers_begin/end, dump_kmers        src/kcount/kmer_dht.cpp:274-307
+ *   kc_owner_of              <- KmerDHT::get_kmer_target_rank                       src/kcount/kmer_dht.cpp:193-196
+ *   kc_lookup                <- KmerDHT::get_local_kmer_counts / kmer_exists /
+ *                               get_kmer_count                                      src/kcount/kmer_dht.cpp:199-245
+ *   kc_get_stats             <- HashTableGPUDriver::get_stats + the stage's reduce_one() counters
+ *                                                                                   src/kcount/kcount_gpu.cpp:294-364
+ *   kc_run                   <- analyze_kmers<MAX_K> (single rank)                  src/kcount/kcount.cpp:143-161
+ *   kc_synth_* / kc_reads_*  <- (no reference counterpart) seeded synthetic PackedRead streams, BASELINE.md section 4
+ *
+ * Semantics are those of the reference's CPU build (src/kcount/kcount_cpu.cpp): N counts as G inside a
+ * k-mer and never as an extension, quality only masks extension bases, the first and last k-mer of a
+ * read are not counted, counts and extension counts saturate at 65535.
+ */
+#ifndef KCOUNT_B200_H
+#define KCOUNT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KC_ABI_VERSION 1
+#define KC_MAX_K 127       /* 4 x u64 key words; k must not be a multiple of 32 */
+#define KC_MAX_KEY_WORDS 4
+
+typedef enum {
+  KC_OK = 0,
+  KC_ERR_ARG = -1,        /* bad argument / call out of order */
+  KC_ERR_CUDA = -2,       /* CUDA runtime error or no device */
+  KC_ERR_NOMEM = -3,      /* device or host allocation failed */
+  KC_ERR_TABLE_FULL = -4, /* a k-mer could not be placed: results undefined, re-run with a larger table */
+  KC_ERR_BINS_FULL = -5,  /* internal: supermer bin overflow that the automatic retry could not fix */
+  KC_ERR_STATE = -6,
+  KC_ERR_IO = -7
+} kc_status;
+
+typedef struct kc_ctx kc_ctx;
+
+/* Stage configuration. Zero-initialise, then kc_config_default(), then override. */
+typedef struct {
+  uint32_t abi_version;      /* KC_ABI_VERSION */
+  uint32_t k;                /* options.hpp:81 kmer_lens */
+  uint32_t m;                /* minimizer length; 0 = reference rule clamp(2k/3+1, 15, 27), kmer_dht.cpp:117-119 */
+  int32_t qual_offset;       /* 33 or 64, options.hpp:85 */
+  int32_t qual_cutoff;       /* KCOUNT_QUAL_CUTOFF = 20, CMakeDefinitions.txt:58 */
+  int32_t dmin_thres;        /* options.hpp:89, default 2 */
+  double dyn_min_depth;      /* DYN_MIN_DEPTH = 0.9, CMakeDefinitions.txt:70 */
+  int32_t use_filter;        /* --use-qf: screen singletons with the two-choice filter before table insertion */
+  int32_t rank;              /* this process' rank (owner id) ... */
+  int32_t n_ranks;           /* ... out of n_ranks owners; 1 = single GPU */
+  int32_t device;            /* CUDA device ordinal, -1 = current */
+  uint64_t est_kmers;        /* my_num_kmers: estimated raw k-mers this rank will receive, contigging.cpp:86 */
+  int32_t sequencing_depth;  /* options.hpp:106, default 4 */
+  double base_error_rate;    /* BASE_ERROR_RATE = 0.005 */
+  uint64_t table_slots;      /* 0 = reference sizing rule (kcount_cpu.cpp:428-470); else exact slot count */
+  uint64_t mem_budget_bytes; /* 0 = 80 % of free device memory */
+  uint32_t local_bins;       /* sub-bins per owner (power of two); 0 = automatic */
+  uint32_t record_bytes;     /* supermer record size 16/32/64; 0 = automatic */
+  uint32_t flags;            /* KC_FLAG_* */
+  uint32_t reserved[7];
+} kc_config;
+
+#define KC_FLAG_KEEP_EXT_COUNTS 1u /* finalize also keeps the 8 extension counters + X/F entries (dump D2) */
+#define KC_FLAG_NO_WARP_DEDUP 2u   /* disable __match_any_sync merging of equal k-mers inside a warp */
+
+/* Counters the reference logs (SURVEY.md section 5 "Metrics") plus what the roofline needs. */
+typedef struct {
+  uint64_t n_reads;            /* reads handed in */
+  uint64_t n_bases;
+  uint64_t raw_kmers;          /* sum(len-k+1), kcount.cpp:86 */
+  uint64_t counted_kmers;      /* sum(max(0,len-k-1)) produced locally = occurrences leaving kc_parse */
+  uint64_t supermers_out;      /* supermer records produced locally */
+  uint64_t supermer_bytes_out; /* bytes of those records */
+  uint64_t supermers_in;       /* records inserted on this rank (KmerDHT::get_num_supermer_inserts) */
+  uint64_t inserted_kmers;     /* occurrences inserted on this rank */
+  uint64_t unique_kmers;       /* distinct keys that reached the table ("Number of elements") */
+  uint64_t filtered_singletons;/* distinct keys stopped by the filter (use_filter only; includes none that recur) */
+  uint64_t ge2_kmers;          /* keys with count >= 2 */
+  uint64_t final_kmers;        /* survivors: count >= 2 and both extensions in ACGT ("Total kmers") */
+  uint64_t purged_kmers;       /* unique_kmers - final_kmers */
+  uint64_t sum_counts;         /* "Total kmer count sum", kcount_cpu.cpp:598 */
+  uint64_t max_count;
+  uint64_t dropped;            /* always 0 on success: a drop is KC_ERR_TABLE_FULL */
+  uint64_t table_slots;        /* capacity actually allocated */
+  uint64_t table_bytes;
+  uint64_t filter_bytes;
+  double avg_kmer_count;       /* sum_counts / final_kmers, rank-local; kcount_cpu.cpp:594-596 */
+  double ms_parse, ms_insert, ms_finalize; /* device time of the last run of each phase (CUDA events) */
+  uint64_t kernel_launches;    /* kernels launched by this context so far */
+} kc_stats;
+
+/* ---- lifecycle ---------------------------------------------------------------------------------- */
+void kc_config_default(kc_config *cfg);
+int kc_create(const kc_config *cfg, kc_ctx **out);
+void kc_destroy(kc_ctx *ctx);
+const char *kc_last_error(const kc_ctx *ctx); /* ctx may be NULL: last error of a failed kc_create */
+const char *kc_version(void);
+int kc_device_count(void);
+
+/* ---- input -------------------------------------------------------------------------------------- */
+/* Append reads. bytes: PackedRead encoding, one byte per base = base(A0 C1 G2 T3 N4) | min(q,31) << 3.
+ * offsets[i] = start of read i inside `bytes`; lens[i] = its length. n_bytes = extent of `bytes`.
+ * Pointers may be host (pageable or pinned) or device memory; the data is copied to the device (async
+ * on the context's stream when pinned/device) and may be released after kc_sync(). */
+int kc_add_reads(kc_ctx *ctx, const uint8_t *bytes, uint64_t n_bytes, const uint64_t *offsets, const uint16_t *lens,
+                 uint64_t n_reads);
+int kc_clear_reads(kc_ctx *ctx);
+
+/* ---- the stage, phase by phase (all asynchronous on the context's stream unless noted) ----------- */
+/* (1)+(2) parse reads, extract minimizers, cut supermers, bin them per owner rank and local bin. */
+int kc_parse(kc_ctx *ctx);
+/* Exchange step. After kc_parse: send_bytes[r] / send_ptr(r) describe the contiguous device buffer of
+ * supermer records destined to owner r (r == rank stays local). The caller moves the data with its own
+ * transport (NCCL all-to-all in this repo; UPC++ RPCs in the reference) into the buffer returned by
+ * kc_exchange_recv_buffer and then calls kc_exchange_done. With n_ranks == 1 none of this is needed. */
+int kc_exchange_send_sizes(kc_ctx *ctx, uint64_t *send_bytes /* [n_ranks] */); /* synchronises the stream */
+int kc_exchange_send_ptr(kc_ctx *ctx, int dst_rank, void **dev_ptr);
+int kc_exchange_recv_buffer(kc_ctx *ctx, const uint64_t *recv_bytes /* [n_ranks] */, void **dev_ptr);
+int kc_exchange_done(kc_ctx *ctx);
+/* (3)+(4) insert every received supermer's k-mers into the table (through the filter when enabled). */
+int kc_insert(kc_ctx *ctx);
+/* (5) purge count<2, resolve extensions, compact survivors. Synchronises and fills stats. */
+int kc_finalize(kc_ctx *ctx, kc_stats *stats);
+/* kc_parse + kc_insert + kc_finalize for n_ranks == 1 == analyze_kmers(). */
+int kc_run(kc_ctx *ctx, kc_stats *stats);
+/* Forget table contents and results but keep reads and allocations (bench loop / iterative k). */
+int kc_reset(kc_ctx *ctx);
+int kc_sync(kc_ctx *ctx);
+int kc_get_stats(kc_ctx *ctx, kc_stats *stats);
+
+/* ---- results ------------------------------------------------------------------------------------ */
+uint32_t kc_key_words(const kc_ctx *ctx); /* N_LONGS = ceil(k/32) */
+/* number of survivors (extended = 0) or of entries with count >= 2 incl. X/F (extended = 1, needs
+ * KC_FLAG_KEEP_EXT_COUNTS). Order of entries is unspecified unless kc_result_sort was called. */
+int kc_result_size(kc_ctx *ctx, int extended, uint64_t *n);
+/* Sort the device-resident result by key words (lexicographic, unsigned) -- the order of dumps D1/D2. */
+int kc_result_sort(kc_ctx *ctx, int extended);
+/* Copy to HOST buffers (any may be NULL): keys[n*N] u64, counts[n] u16, left[n]/right[n] chars in
+ * ACGT (or X/F when extended), ext8[n*8] u16 = lA lC lG lT rA rC rG rT (extended only). */
+int kc_result_copy(kc_ctx *ctx, int extended, uint64_t *keys, uint16_t *counts, char *left, char *right, uint16_t *ext8);
+/* Device pointers of the same arrays (valid until kc_reset/kc_destroy). */
+int kc_result_device_ptrs(kc_ctx *ctx, int extended, const uint64_t **keys, const uint16_t **counts, const char **left,
+                          const char **right, const uint16_t **ext8);
+/* 64-bit order-independent checksum of the result (sum over entries of a mix of key words, count, L, R
+ * and, when extended, the 8 ext counters); computed on the device. Same function in oracle/. */
+int kc_result_checksum(kc_ctx *ctx, int extended, uint64_t *checksum);
+/* Text dump, one "KMER count L R" line per survivor, sorted by key (kmer_dht.cpp:274-297 writes the same
+ * lines unsorted and gzipped). extended adds the 8 counters. */
+int kc_dump_sorted(kc_ctx *ctx, const char *path, int extended);
+/* Batched lookup in the finalized result: keys[n*N] HOST canonical k-mers -> counts (0 = absent), L, R. */
+int kc_lookup(kc_ctx *ctx, const uint64_t *keys, uint64_t n, uint16_t *counts, char *left, char *right);
+/* Owner rank of a canonical k-mer (key_words[N]) under this context's m and n_ranks. Host-side, no GPU. */
+int kc_owner_of(const kc_ctx *ctx, const uint64_t *key_words);
+uint32_t kc_minimizer_len(const kc_ctx *ctx);
+
+/* ---- host helpers: pinned memory, synthetic reads, read files ------------------------------------ */
+int kc_host_alloc(void **ptr, size_t bytes); /* cudaHostAlloc */
+int kc_host_free(void *ptr);
+
+typedef struct {
+  uint64_t seed;
+  uint32_t n_genomes;
+  uint64_t genome_len_min, genome_len_max; /* uniform */
+  double abundance_sigma;                  /* lognormal(0, sigma) coverage per genome; 0 = equal */
+  uint32_t read_len, read_len_min;         /* read_len_min == 0 -> fixed length */
+  double sub_rate;                         /* substitution probability per base */
+  double lowq_rate, lowq_rate_sub;         /* P(quality '+') on correct / substituted bases (0.02 / 0.5) */
+  double n_rate;                           /* P(base reported as N); 0 in every BASELINE config */
+  int32_t paired;                          /* 1: reads 2i,2i+1 are mates (fwd/rev) of one fragment */
+  double insert_mean, insert_sd;
+  int32_t qual_offset;
+  uint32_t reserved[5];
+} kc_synth_config;
+typedef struct kc_synth kc_synth;
+void kc_synth_config_default(kc_synth_config *cfg); /* config C1 of BASELINE.md with seed 1001 */
+int kc_synth_create(const kc_synth_config *cfg, kc_synth **out);
+void kc_synth_destroy(kc_synth *s);
+/* reads [first, first+n) of the infinite seeded stream; read i depends only on (seed, i). bytes must hold
+ * n*read_len; offsets/lens hold n entries; offsets are relative to bytes. Returns bytes used in *n_bytes. */
+int kc_synth_generate(const kc_synth *s, uint64_t first, uint64_t n, uint8_t *bytes, uint64_t *offsets, uint16_t *lens,
+                      uint64_t *n_bytes, int n_threads);
+int kc_reads_save(const char *path, const uint8_t *bytes, uint64_t n_bytes, const uint64_t *offsets, const uint16_t *lens,
+                  uint64_t n_reads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KCOUNT_B200_H */
