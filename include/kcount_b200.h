@@ -140,6 +140,8 @@ int kc_parse(kc_ctx *ctx);
 int kc_exchange_send_sizes(kc_ctx *ctx, uint64_t *send_bytes /* [n_ranks] */); /* synchronises the stream */
 int kc_exchange_send_ptr(kc_ctx *ctx, int dst_rank, void **dev_ptr);
 int kc_exchange_recv_buffer(kc_ctx *ctx, const uint64_t *recv_bytes /* [n_ranks] */, void **dev_ptr);
+/* byte offset of each source rank's block inside the receive buffer (256-byte aligned) */
+int kc_exchange_recv_offsets(kc_ctx *ctx, uint64_t *offsets /* [n_ranks] */);
 int kc_exchange_done(kc_ctx *ctx);
 /* (3)+(4) insert every received supermer's k-mers into the table (through the filter when enabled). */
 int kc_insert(kc_ctx *ctx);

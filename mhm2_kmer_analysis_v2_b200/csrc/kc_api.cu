@@ -1,0 +1,1012 @@
+// kc_api.cu -- context, memory and phase orchestration behind the C ABI of include/kcount_b200.h.
+// Host C++ only calls CUDA from here; no CUDA type crosses the ABI. There is no CPU fallback anywhere: every phase is a
+// kernel launch on the context's stream.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+#include <string>
+#include <vector>
+
+#include "kc_internal.h"
+#include "kcount_b200.h"
+
+namespace kc {
+int parse_grid_size(uint64_t n_reads, uint32_t read_stride, int sm_count);
+int parse_resv_records();
+int parse_warps_per_block();
+}  // namespace kc
+
+using namespace kc;
+
+static thread_local std::string g_create_error;
+
+struct ReadChunk {
+  uint8_t *d_bytes = nullptr;
+  uint64_t *d_offsets = nullptr;
+  uint16_t *d_lens = nullptr;
+  uint64_t n_reads = 0, n_bytes = 0;
+};
+
+enum Phase { PH_EMPTY = 0, PH_PARSED, PH_RECV_READY, PH_INSERTED, PH_FINALIZED };
+
+struct ResultSet {
+  uint64_t *keys = nullptr;
+  uint16_t *counts = nullptr, *ext8 = nullptr;
+  char *left = nullptr, *right = nullptr;
+  uint64_t n = 0, cap = 0;
+  bool sorted = false;
+};
+
+struct kc_ctx {
+  kc_config cfg;
+  int k = 0, m = 0, N = 0, rec_bytes = 0, P = 1, G = 1, rank = 0;
+  uint32_t n_ids = 1;
+  int device = 0, sm_count = 148;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::string err;
+  Phase phase = PH_EMPTY;
+
+  std::vector<ReadChunk> chunks;
+  uint64_t n_reads = 0, n_bases = 0;
+
+  // supermer bins (send side)
+  uint8_t *d_bins = nullptr;
+  uint64_t bins_bytes = 0, bins_alloc = 0;
+  int header_bytes = 0;
+  std::vector<uint64_t> h_bin_base, h_bin_first, h_bin_cap, h_region_off, h_region_bytes;
+  std::vector<unsigned long long> h_cursor;
+  uint64_t *d_bin_base = nullptr, *d_bin_first = nullptr, *d_bin_cap = nullptr;
+  unsigned long long *d_cursor = nullptr;
+  uint8_t **d_hdr_ptrs = nullptr;
+  bool caps_valid = false;
+
+  // receive side
+  uint8_t *d_recv = nullptr;
+  uint64_t recv_alloc = 0;
+  std::vector<uint64_t> recv_off, recv_bytes;
+  uint8_t **d_src_ptr = nullptr;
+  Segment *d_segments = nullptr;
+  uint32_t *d_seg_tile_start = nullptr;
+  Region *d_regions = nullptr;
+  unsigned long long *d_total_records = nullptr;
+
+  // table
+  SlotA *d_A = nullptr;
+  uint64_t *d_B = nullptr;
+  uint64_t table_slots = 0, table_alloc_slots = 0;
+  uint32_t *d_filter = nullptr;
+  uint64_t filter_buckets = 0, filter_alloc_buckets = 0;
+  Overflow ovf{nullptr, nullptr, 0};
+  uint64_t ovf_alloc = 0;
+
+  DevCounters *d_ctr = nullptr;
+  DevCounters h_ctr;
+
+  ResultSet res_final, res_ext;
+  kc_stats stats;
+  uint64_t launches = 0;
+};
+
+// ------------------------------------------------------------------------------------------------ helpers
+static int fail(kc_ctx *c, int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (c)
+    c->err = buf;
+  else
+    g_create_error = buf;
+  return code;
+}
+
+#define CK(call)                                                                                           \
+  do {                                                                                                     \
+    cudaError_t e_ = (call);                                                                               \
+    if (e_ != cudaSuccess)                                                                                 \
+      return fail(c, e_ == cudaErrorMemoryAllocation ? KC_ERR_NOMEM : KC_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, \
+                  cudaGetErrorString(e_));                                                                 \
+  } while (0)
+
+template <typename T>
+static cudaError_t dev_alloc(T **p, uint64_t count) {
+  return cudaMalloc((void **)p, std::max<uint64_t>(count, 1) * sizeof(T));
+}
+template <typename T>
+static void dev_free(T *&p) {
+  if (p) cudaFree(p);
+  p = nullptr;
+}
+
+static int reference_minimizer_len(int k) {  // KmerDHT::KmerDHT, src/kcount/kmer_dht.cpp:117-119
+  int m = k * 2 / 3 + 1;
+  if (m < 15) m = 15;
+  if (m > 27) m = 27;
+  return m;
+}
+
+static int auto_record_bytes(int k, int m, int n_ids) {
+  if (n_ids == 1) return 64;  // no owner/bin cuts: a record carries up to 160 - k - 1 k-mers of a read
+  int w = k - m + 1;          // expected supermer ~ (w + 1) / 2 k-mers; leave room for about twice that
+  int want = k + 1 + (w + 1);
+  if (want <= 32) return 16;
+  if (want <= 80) return 32;
+  return 64;
+}
+
+// ------------------------------------------------------------------------------------------------ lifecycle
+extern "C" void kc_config_default(kc_config *cfg) {
+  memset(cfg, 0, sizeof *cfg);
+  cfg->abi_version = KC_ABI_VERSION;
+  cfg->k = 21;
+  cfg->m = 0;
+  cfg->qual_offset = 33;
+  cfg->qual_cutoff = 20;
+  cfg->dmin_thres = 2;
+  cfg->dyn_min_depth = 0.9;
+  cfg->use_filter = 0;
+  cfg->rank = 0;
+  cfg->n_ranks = 1;
+  cfg->device = -1;
+  cfg->est_kmers = 0;
+  cfg->sequencing_depth = 4;
+  cfg->base_error_rate = 0.005;
+}
+
+extern "C" const char *kc_version(void) { return "kcount_b200 0.1 (sm_100a)"; }
+
+extern "C" int kc_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+extern "C" const char *kc_last_error(const kc_ctx *c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
+  kc_ctx *c = nullptr;
+  if (!cfg || !out) return fail(c, KC_ERR_ARG, "kc_create: null argument");
+  if (cfg->abi_version != KC_ABI_VERSION) return fail(c, KC_ERR_ARG, "kc_create: ABI version %u != %u", cfg->abi_version, KC_ABI_VERSION);
+  if (cfg->k < 2 || cfg->k > KC_MAX_K || cfg->k % 32 == 0)
+    return fail(c, KC_ERR_ARG, "kc_create: k=%u unsupported (2..%d, not a multiple of 32)", cfg->k, KC_MAX_K);
+  if (cfg->n_ranks < 1 || cfg->rank < 0 || cfg->rank >= cfg->n_ranks) return fail(c, KC_ERR_ARG, "kc_create: bad rank %d/%d", cfg->rank, cfg->n_ranks);
+  int m = cfg->m ? (int)cfg->m : reference_minimizer_len(cfg->k);
+  if (m > (int)cfg->k) m = cfg->k;
+  if (m < 1 || m > 31) return fail(c, KC_ERR_ARG, "kc_create: minimizer length %d unsupported (1..31)", m);
+  uint32_t P = cfg->local_bins ? cfg->local_bins : 1;
+  if (P & (P - 1)) return fail(c, KC_ERR_ARG, "kc_create: local_bins must be a power of two");
+  if ((uint64_t)P * cfg->n_ranks > 65536) return fail(c, KC_ERR_ARG, "kc_create: too many bins");
+  int n_ids = (int)(P * cfg->n_ranks);
+  int R = cfg->record_bytes ? (int)cfg->record_bytes : auto_record_bytes(cfg->k, m, n_ids);
+  if (R != 16 && R != 32 && R != 64) return fail(c, KC_ERR_ARG, "kc_create: record_bytes must be 16, 32 or 64");
+  while (record_geom(R, cfg->k).max_kmers < 1 && R < 64) R *= 2;
+  if (record_geom(R, cfg->k).max_kmers < 1) return fail(c, KC_ERR_ARG, "kc_create: k too large for a 64-byte record");
+
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(c, KC_ERR_CUDA, "kc_create: no CUDA device (%s); this library has no CPU path", cudaGetErrorString(e));
+  c = new kc_ctx();
+  c->cfg = *cfg;
+  c->k = cfg->k;
+  c->m = m;
+  c->N = (cfg->k + 31) / 32;
+  c->rec_bytes = R;
+  c->P = P;
+  c->G = cfg->n_ranks;
+  c->rank = cfg->rank;
+  c->n_ids = n_ids;
+  memset(&c->stats, 0, sizeof c->stats);
+  memset(&c->h_ctr, 0, sizeof c->h_ctr);
+  int dev = cfg->device;
+  if (dev < 0) cudaGetDevice(&dev);
+  c->device = dev;
+  auto bail = [&](cudaError_t ee, const char *what) {
+    int code = fail(nullptr, KC_ERR_CUDA, "kc_create: %s: %s", what, cudaGetErrorString(ee));
+    delete c;
+    return code;
+  };
+  if ((e = cudaSetDevice(dev)) != cudaSuccess) return bail(e, "cudaSetDevice");
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, dev)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
+  c->sm_count = prop.multiProcessorCount;
+  if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  cudaEventCreate(&c->ev0);
+  cudaEventCreate(&c->ev1);
+  if ((e = dev_alloc(&c->d_ctr, 1)) != cudaSuccess) return bail(e, "cudaMalloc");
+  cudaMemsetAsync(c->d_ctr, 0, sizeof(DevCounters), c->stream);
+  c->header_bytes = ((c->P * 8 + kHeaderAlign - 1) / kHeaderAlign) * kHeaderAlign;
+  *out = c;
+  return KC_OK;
+}
+
+static void free_results(ResultSet &r) {
+  dev_free(r.keys);
+  dev_free(r.counts);
+  dev_free(r.ext8);
+  dev_free(r.left);
+  dev_free(r.right);
+  r.n = r.cap = 0;
+  r.sorted = false;
+}
+
+extern "C" int kc_clear_reads(kc_ctx *c) {
+  if (!c) return KC_ERR_ARG;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  for (auto &ch : c->chunks) {
+    dev_free(ch.d_bytes);
+    dev_free(ch.d_offsets);
+    dev_free(ch.d_lens);
+  }
+  c->chunks.clear();
+  c->n_reads = c->n_bases = 0;
+  c->caps_valid = false;
+  c->phase = PH_EMPTY;
+  return KC_OK;
+}
+
+extern "C" void kc_destroy(kc_ctx *c) {
+  if (!c) return;
+  kc_clear_reads(c);
+  dev_free(c->d_bins);
+  dev_free(c->d_bin_base);
+  dev_free(c->d_bin_first);
+  dev_free(c->d_bin_cap);
+  dev_free(c->d_cursor);
+  dev_free(c->d_hdr_ptrs);
+  dev_free(c->d_recv);
+  dev_free(c->d_src_ptr);
+  dev_free(c->d_segments);
+  dev_free(c->d_seg_tile_start);
+  dev_free(c->d_regions);
+  dev_free(c->d_total_records);
+  dev_free(c->d_A);
+  dev_free(c->d_B);
+  dev_free(c->d_filter);
+  dev_free(c->ovf.keys);
+  dev_free(c->ovf.ext);
+  dev_free(c->d_ctr);
+  free_results(c->res_final);
+  free_results(c->res_ext);
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+extern "C" int kc_sync(kc_ctx *c) {
+  if (!c) return KC_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  return KC_OK;
+}
+
+extern "C" uint32_t kc_key_words(const kc_ctx *c) { return c ? c->N : 0; }
+extern "C" uint32_t kc_minimizer_len(const kc_ctx *c) { return c ? c->m : 0; }
+
+extern "C" int kc_host_alloc(void **ptr, size_t bytes) {
+  return cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocDefault) == cudaSuccess ? KC_OK : KC_ERR_NOMEM;
+}
+extern "C" int kc_host_free(void *ptr) { return cudaFreeHost(ptr) == cudaSuccess ? KC_OK : KC_ERR_CUDA; }
+
+// ------------------------------------------------------------------------------------------------ input
+extern "C" int kc_add_reads(kc_ctx *c, const uint8_t *bytes, uint64_t n_bytes, const uint64_t *offsets, const uint16_t *lens,
+                            uint64_t n_reads) {
+  if (!c || (n_reads && (!bytes || !offsets || !lens))) return fail(c, KC_ERR_ARG, "kc_add_reads: null argument");
+  if (n_reads == 0) return KC_OK;
+  CK(cudaSetDevice(c->device));
+  ReadChunk ch;
+  ch.n_reads = n_reads;
+  ch.n_bytes = n_bytes;
+  CK(dev_alloc(&ch.d_bytes, n_bytes + 16));
+  CK(dev_alloc(&ch.d_offsets, n_reads));
+  CK(dev_alloc(&ch.d_lens, n_reads));
+  // cudaMemcpyDefault: host (pageable or pinned) and device sources alike
+  CK(cudaMemcpyAsync(ch.d_bytes, bytes, n_bytes, cudaMemcpyDefault, c->stream));
+  CK(cudaMemcpyAsync(ch.d_offsets, offsets, n_reads * sizeof(uint64_t), cudaMemcpyDefault, c->stream));
+  CK(cudaMemcpyAsync(ch.d_lens, lens, n_reads * sizeof(uint16_t), cudaMemcpyDefault, c->stream));
+  c->chunks.push_back(ch);
+  c->n_reads += n_reads;
+  c->n_bases += n_bytes;
+  c->caps_valid = false;
+  c->phase = PH_EMPTY;
+  return KC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ parse
+static ParseParams parse_params(kc_ctx *c, const ReadChunk &ch, uint32_t stride, int count_only) {
+  ParseParams p;
+  memset(&p, 0, sizeof p);
+  p.bytes = ch.d_bytes;
+  p.offsets = ch.d_offsets;
+  p.lens = ch.d_lens;
+  p.n_reads = ch.n_reads;
+  p.read_stride = stride;
+  p.count_only = count_only;
+  p.k = c->k;
+  p.m = c->m;
+  p.qual_cutoff = c->cfg.qual_cutoff;
+  p.rec_bytes = c->rec_bytes;
+  p.n_ids = c->n_ids;
+  p.bins_mask = c->P - 1;
+  p.div_ranks = make_fastdiv(c->G);
+  p.bins = c->d_bins;
+  p.bin_base = c->d_bin_base;
+  p.bin_cap = c->d_bin_cap;
+  p.bin_cursor = c->d_cursor;
+  p.ctr = c->d_ctr;
+  return p;
+}
+
+// lay the bins out: per owner [header block][bin 0 records][bin 1 records]..., given per-bin capacities in records
+static int layout_bins(kc_ctx *c, const std::vector<uint64_t> &cap) {
+  const uint32_t n = c->n_ids;
+  c->h_bin_base.assign(n, 0);
+  c->h_bin_first.assign(n, 0);
+  c->h_bin_cap = cap;
+  c->h_region_off.assign(c->G, 0);
+  c->h_region_bytes.assign(c->G, 0);
+  uint64_t at = 0;
+  std::vector<uint8_t *> hdr(c->G);
+  for (int o = 0; o < c->G; o++) {
+    c->h_region_off[o] = at;
+    at += c->header_bytes;
+    uint64_t first = 0;
+    for (int b = 0; b < c->P; b++) {
+      uint32_t id = o * c->P + b;
+      if (first + cap[id] > 0xffffffffULL) return fail(c, KC_ERR_ARG, "supermer region too large for 32-bit record index; use more local bins/ranks");
+      c->h_bin_first[id] = first;
+      c->h_bin_base[id] = at + first * c->rec_bytes;
+      first += cap[id];
+    }
+    at += first * c->rec_bytes;
+    at = (at + 255) & ~255ULL;
+    c->h_region_bytes[o] = at - c->h_region_off[o];
+  }
+  c->bins_bytes = at;
+  if (at > c->bins_alloc) {
+    dev_free(c->d_bins);
+    uint64_t want = at + at / 16;
+    CK(dev_alloc(&c->d_bins, want));
+    c->bins_alloc = want;
+  }
+  if (!c->d_bin_base) {
+    CK(dev_alloc(&c->d_bin_base, n));
+    CK(dev_alloc(&c->d_bin_first, n));
+    CK(dev_alloc(&c->d_bin_cap, n));
+    CK(dev_alloc(&c->d_cursor, n));
+    CK(dev_alloc(&c->d_hdr_ptrs, c->G));
+  }
+  for (int o = 0; o < c->G; o++) hdr[o] = c->d_bins + c->h_region_off[o];
+  CK(cudaMemcpyAsync(c->d_bin_base, c->h_bin_base.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->d_bin_first, c->h_bin_first.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->d_bin_cap, c->h_bin_cap.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->d_hdr_ptrs, hdr.data(), c->G * sizeof(uint8_t *), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));  // host vectors above are reused
+  return KC_OK;
+}
+
+static uint64_t reservation_pad(kc_ctx *c) {
+  if (c->n_ids > 32) return 64;
+  uint64_t pad = parse_resv_records();
+  for (auto &ch : c->chunks)
+    pad += (uint64_t)parse_grid_size(ch.n_reads, 1, c->sm_count) * parse_warps_per_block() * parse_resv_records();
+  return pad;
+}
+
+// capacity estimate from a strided sample of the reads (count-only run of the parse kernel)
+static int estimate_caps(kc_ctx *c) {
+  const uint32_t n = c->n_ids;
+  if (!c->d_cursor) {
+    std::vector<uint64_t> zero(n, 0);
+    int rc = layout_bins(c, zero);
+    if (rc) return rc;
+  }
+  uint32_t stride = (uint32_t)std::max<uint64_t>(1, c->n_reads / 262144);
+  CK(cudaMemsetAsync(c->d_cursor, 0, n * sizeof(unsigned long long), c->stream));
+  for (auto &ch : c->chunks) {
+    ParseParams p = parse_params(c, ch, stride, 1);
+    CK(launch_parse(p, c->sm_count, c->stream, &c->launches));
+  }
+  c->h_cursor.assign(n, 0);
+  CK(cudaMemcpyAsync(c->h_cursor.data(), c->d_cursor, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  std::vector<uint64_t> cap(n);
+  const uint64_t pad = reservation_pad(c);
+  for (uint32_t i = 0; i < n; i++) {
+    double cnt = (double)c->h_cursor[i];
+    double est = cnt * stride;
+    if (stride > 1) est += 6.0 * stride * std::sqrt(cnt + 1.0) + 0.02 * est;
+    if (c->n_ids <= 32) est *= 1.15;  // reservation tails (kc_parse.cu)
+    cap[i] = (uint64_t)est + pad;
+  }
+  int rc = layout_bins(c, cap);
+  if (rc) return rc;
+  c->caps_valid = true;
+  return KC_OK;
+}
+
+static int run_parse(kc_ctx *c) {
+  const uint32_t n = c->n_ids;
+  CK(cudaMemsetAsync(c->d_cursor, 0, n * sizeof(unsigned long long), c->stream));
+  CK(cudaMemsetAsync(&c->d_ctr->parse_counted, 0, 3 * sizeof(unsigned long long) + sizeof(unsigned int), c->stream));
+  for (auto &ch : c->chunks) {
+    ParseParams p = parse_params(c, ch, 1, 0);
+    CK(launch_parse(p, c->sm_count, c->stream, &c->launches));
+  }
+  CK(launch_write_headers(c->d_hdr_ptrs, c->d_bin_first, c->d_cursor, c->d_bin_cap, c->G, c->P, c->stream, &c->launches));
+  c->h_cursor.assign(n, 0);
+  CK(cudaMemcpyAsync(c->h_cursor.data(), c->d_cursor, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  return KC_OK;
+}
+
+extern "C" int kc_parse(kc_ctx *c) {
+  if (!c) return KC_ERR_ARG;
+  if (c->chunks.empty()) return fail(c, KC_ERR_STATE, "kc_parse: no reads");
+  CK(cudaSetDevice(c->device));
+  CK(cudaEventRecord(c->ev0, c->stream));
+  if (!c->caps_valid) {
+    int rc = estimate_caps(c);
+    if (rc) return rc;
+  }
+  int rc = run_parse(c);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(c->stream));
+  if (c->h_ctr.err_bins_full) {
+    // the sample under-estimated a bin: the cursors now hold the exact demand, lay out again and redo
+    std::vector<uint64_t> cap(c->n_ids);
+    const uint64_t pad = reservation_pad(c);
+    for (uint32_t i = 0; i < c->n_ids; i++) cap[i] = (c->n_ids <= 32 ? 2 : 1) * c->h_cursor[i] + pad;
+    rc = layout_bins(c, cap);
+    if (rc) return rc;
+    rc = run_parse(c);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(c->stream));
+    if (c->h_ctr.err_bins_full) return fail(c, KC_ERR_BINS_FULL, "kc_parse: supermer bins overflowed after exact re-layout");
+  }
+  CK(cudaEventRecord(c->ev1, c->stream));
+  CK(cudaEventSynchronize(c->ev1));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+  c->stats.ms_parse = ms;
+  c->stats.n_reads = c->n_reads;
+  c->stats.n_bases = c->n_bases;
+  c->stats.raw_kmers = c->h_ctr.parse_raw;
+  c->stats.counted_kmers = c->h_ctr.parse_counted;
+  c->stats.supermers_out = c->h_ctr.parse_records;
+  c->stats.supermer_bytes_out = c->h_ctr.parse_records * c->rec_bytes;
+  c->phase = PH_PARSED;
+  c->recv_off.clear();
+  return KC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ exchange
+static uint64_t used_region_bytes(kc_ctx *c, int o) {
+  // header + records up to the end of the last non-empty bin (the slack behind it need not travel)
+  uint64_t end = 0;
+  for (int b = 0; b < c->P; b++) {
+    uint32_t id = o * c->P + b;
+    uint64_t cnt = std::min<uint64_t>(c->h_cursor[id], c->h_bin_cap[id]);
+    if (cnt) end = std::max(end, c->h_bin_first[id] + cnt);
+  }
+  return c->header_bytes + end * c->rec_bytes;
+}
+
+extern "C" int kc_exchange_send_sizes(kc_ctx *c, uint64_t *send_bytes) {
+  if (!c || !send_bytes) return KC_ERR_ARG;
+  if (c->phase != PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_send_sizes: call kc_parse first");
+  for (int o = 0; o < c->G; o++) send_bytes[o] = (o == c->rank) ? 0 : used_region_bytes(c, o);
+  return KC_OK;
+}
+
+extern "C" int kc_exchange_send_ptr(kc_ctx *c, int dst, void **dev_ptr) {
+  if (!c || !dev_ptr || dst < 0 || dst >= c->G) return KC_ERR_ARG;
+  if (c->phase != PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_send_ptr: call kc_parse first");
+  *dev_ptr = c->d_bins + c->h_region_off[dst];
+  return KC_OK;
+}
+
+extern "C" int kc_exchange_recv_buffer(kc_ctx *c, const uint64_t *recv_bytes, void **dev_ptr) {
+  if (!c || !recv_bytes || !dev_ptr) return KC_ERR_ARG;
+  if (c->phase != PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_recv_buffer: call kc_parse first");
+  CK(cudaSetDevice(c->device));
+  c->recv_off.assign(c->G, 0);
+  c->recv_bytes.assign(recv_bytes, recv_bytes + c->G);
+  uint64_t at = 0;
+  for (int s = 0; s < c->G; s++) {
+    c->recv_off[s] = at;
+    if (s == c->rank) c->recv_bytes[s] = 0;
+    at += (c->recv_bytes[s] + 255) & ~255ULL;
+  }
+  if (at > c->recv_alloc) {
+    dev_free(c->d_recv);
+    CK(dev_alloc(&c->d_recv, at + at / 16 + 256));
+    c->recv_alloc = at + at / 16 + 256;
+  }
+  *dev_ptr = c->d_recv;
+  return KC_OK;
+}
+
+extern "C" int kc_exchange_done(kc_ctx *c) {
+  if (!c) return KC_ERR_ARG;
+  if (c->phase != PH_PARSED || (int)c->recv_off.size() != c->G) return fail(c, KC_ERR_STATE, "kc_exchange_done: no receive buffer");
+  c->phase = PH_RECV_READY;
+  return KC_OK;
+}
+
+// byte offset of source s inside the receive buffer (the caller's all-to-all needs the displacements)
+extern "C" int kc_exchange_recv_offsets(kc_ctx *c, uint64_t *offsets) {
+  if (!c || !offsets || (int)c->recv_off.size() != c->G) return KC_ERR_ARG;
+  for (int s = 0; s < c->G; s++) offsets[s] = c->recv_off[s];
+  return KC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ insert
+static uint64_t reference_table_slots(kc_ctx *c, uint64_t est_kmers) {
+  // KmerDHT::KmerDHT + HashTableInserter::init: (kmers / depth + kmers * (1 - (1 - err)^k)) / 0.66
+  // (src/kcount/kmer_dht.cpp:126-131, src/kcount/kcount_cpu.cpp:443-446); with the filter only the first term needs slots
+  double depth = c->cfg.sequencing_depth > 0 ? c->cfg.sequencing_depth : 4;
+  double kmer_err = 1.0 - std::pow(1.0 - c->cfg.base_error_rate, (double)c->k);
+  double elems = (double)est_kmers / depth;
+  if (!c->cfg.use_filter) elems += (double)est_kmers * kmer_err;
+  return (uint64_t)(elems / 0.66) + 1024;
+}
+
+static int ensure_table(kc_ctx *c) {
+  uint64_t est = c->cfg.est_kmers ? c->cfg.est_kmers : std::max<uint64_t>(c->h_ctr.parse_raw, 1024);
+  uint64_t slots = c->cfg.table_slots ? c->cfg.table_slots : reference_table_slots(c, est);
+  if (c->table_slots > slots) slots = c->table_slots;  // grown by a retry
+  slots = std::max<uint64_t>(slots, 128ull * c->P + 1024);
+  uint64_t buckets = 0;
+  if (c->cfg.use_filter) {
+    double kmer_err = 1.0 - std::pow(1.0 - c->cfg.base_error_rate, (double)c->k);
+    double depth = c->cfg.sequencing_depth > 0 ? c->cfg.sequencing_depth : 4;
+    double distinct = (double)est / depth + (double)est * kmer_err;
+    buckets = (uint64_t)(distinct / 0.75 / 16.0) + 8ull * c->P + 64;
+  }
+  // memory budget
+  size_t free_b = 0, total_b = 0;
+  CK(cudaMemGetInfo(&free_b, &total_b));
+  uint64_t have = (uint64_t)c->table_alloc_slots * (32 + 8 * (c->N - 1)) + c->filter_alloc_buckets * 32;
+  uint64_t budget = c->cfg.mem_budget_bytes ? c->cfg.mem_budget_bytes : (uint64_t)((free_b + have) * 0.8);
+  uint64_t per_slot = 32 + 8 * (c->N - 1);
+  if (buckets * 32 + slots * per_slot > budget) {
+    if (c->cfg.table_slots) return fail(c, KC_ERR_NOMEM, "table of %llu slots does not fit the memory budget", (unsigned long long)slots);
+    uint64_t fit = (budget - std::min(budget, buckets * 32)) / per_slot;
+    if (fit < 128ull * c->P + 1024) return fail(c, KC_ERR_NOMEM, "no room for the k-mer table");
+    slots = fit;
+  }
+  if (slots > c->table_alloc_slots) {
+    dev_free(c->d_A);
+    dev_free(c->d_B);
+    CK(dev_alloc(&c->d_A, slots));
+    if (c->N > 1) CK(dev_alloc(&c->d_B, slots * (c->N - 1)));
+    c->table_alloc_slots = slots;
+  }
+  c->table_slots = slots;
+  if (buckets > c->filter_alloc_buckets) {
+    dev_free(c->d_filter);
+    CK(dev_alloc(&c->d_filter, buckets * 8));
+    c->filter_alloc_buckets = buckets;
+  }
+  c->filter_buckets = buckets;
+  // overflow side table: a key needs >= 65535 occurrences to get an entry
+  uint64_t occ = std::max<uint64_t>(c->h_ctr.parse_counted * (uint64_t)c->G, 1);
+  uint64_t want = 1024;
+  while (want < 4 * (occ / 65535 + 1)) want *= 2;
+  if (want > c->ovf_alloc) {
+    dev_free(c->ovf.keys);
+    dev_free(c->ovf.ext);
+    CK(dev_alloc(&c->ovf.keys, want));
+    CK(dev_alloc(&c->ovf.ext, want * 8));
+    c->ovf_alloc = want;
+  }
+  c->ovf.mask = c->ovf_alloc - 1;
+  return KC_OK;
+}
+
+extern "C" int kc_insert(kc_ctx *c) {
+  if (!c) return KC_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  if (c->G == 1) {
+    if (c->phase < PH_PARSED) return fail(c, KC_ERR_STATE, "kc_insert: call kc_parse first");
+  } else if (c->phase != PH_RECV_READY && c->phase != PH_INSERTED && c->phase != PH_FINALIZED) {
+    return fail(c, KC_ERR_STATE, "kc_insert: exchange not completed (kc_exchange_done)");
+  }
+  int rc = ensure_table(c);
+  if (rc) return rc;
+  const int n_seg = c->P * c->G;
+  if (!c->d_src_ptr) {
+    CK(dev_alloc(&c->d_src_ptr, c->G));
+    CK(dev_alloc(&c->d_segments, n_seg));
+    CK(dev_alloc(&c->d_seg_tile_start, n_seg + 1));
+    CK(dev_alloc(&c->d_regions, c->P));
+    CK(dev_alloc(&c->d_total_records, 1));
+  }
+  std::vector<uint8_t *> src(c->G, nullptr);
+  for (int s = 0; s < c->G; s++) {
+    if (s == c->rank)
+      src[s] = c->d_bins + c->h_region_off[c->rank];
+    else
+      src[s] = c->recv_bytes[s] ? c->d_recv + c->recv_off[s] : nullptr;
+  }
+  CK(cudaMemcpyAsync(c->d_src_ptr, src.data(), c->G * sizeof(uint8_t *), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+
+  CK(cudaEventRecord(c->ev0, c->stream));
+  // clear table, filter, overflow table and the insert-side counters
+  CK(cudaMemsetAsync(c->d_A, 0, c->table_slots * sizeof(SlotA), c->stream));
+  if (c->filter_buckets) CK(cudaMemsetAsync(c->d_filter, 0, c->filter_buckets * 32, c->stream));
+  CK(cudaMemsetAsync(c->ovf.keys, 0, c->ovf_alloc * 8, c->stream));
+  CK(cudaMemsetAsync(c->ovf.ext, 0, c->ovf_alloc * 32, c->stream));
+  CK(cudaMemsetAsync(c->d_ctr, 0, offsetof(DevCounters, parse_counted), c->stream));
+
+  PlanParams pp;
+  pp.n_src = c->G;
+  pp.local_bins = c->P;
+  pp.rec_bytes = c->rec_bytes;
+  pp.tile_records = kTileRecords;
+  pp.src_ptr = c->d_src_ptr;
+  pp.segments = c->d_segments;
+  pp.seg_tile_start = c->d_seg_tile_start;
+  pp.regions = c->d_regions;
+  pp.table_slots = c->table_slots;
+  pp.filter_buckets = c->filter_buckets;
+  pp.total_records = c->d_total_records;
+  CK(launch_plan(pp, c->stream, &c->launches));
+
+  InsertParams ip;
+  memset(&ip, 0, sizeof ip);
+  ip.k = c->k;
+  ip.rec_bytes = c->rec_bytes;
+  ip.n_segments = n_seg;
+  ip.segments = c->d_segments;
+  ip.seg_tile_start = c->d_seg_tile_start;
+  ip.regions = c->d_regions;
+  ip.A = c->d_A;
+  ip.B = c->d_B;
+  ip.filter = c->d_filter;
+  ip.ovf = c->ovf;
+  ip.ctr = c->d_ctr;
+  const bool dedup = !(c->cfg.flags & KC_FLAG_NO_WARP_DEDUP);
+  if (!c->cfg.use_filter) {
+    CK(launch_insert(ip, c->N, MODE_INSERT, dedup, c->sm_count, c->stream, &c->launches));
+  } else {
+    // exact singleton screen: pass A admits keys seen at least twice, pass B counts only admitted keys
+    CK(launch_insert(ip, c->N, MODE_ADMIT, dedup, c->sm_count, c->stream, &c->launches));
+    CK(cudaMemsetAsync(&c->d_ctr->tile_cursor, 0, sizeof(unsigned long long), c->stream));
+    CK(launch_insert(ip, c->N, MODE_UPDATE, dedup, c->sm_count, c->stream, &c->launches));
+  }
+  CK(cudaEventRecord(c->ev1, c->stream));
+  c->phase = PH_INSERTED;
+  free_results(c->res_final);
+  free_results(c->res_ext);
+  return KC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ finalize
+static int alloc_results(kc_ctx *c, ResultSet &r, uint64_t cap, bool with_ext) {
+  free_results(r);
+  r.cap = cap;
+  CK(dev_alloc(&r.keys, cap * c->N));
+  CK(dev_alloc(&r.counts, cap));
+  CK(dev_alloc(&r.left, cap));
+  CK(dev_alloc(&r.right, cap));
+  if (with_ext) CK(dev_alloc(&r.ext8, cap * 8));
+  return KC_OK;
+}
+
+static void fill_stats(kc_ctx *c) {
+  kc_stats &s = c->stats;
+  const DevCounters &h = c->h_ctr;
+  s.supermers_in = h.records_in;
+  s.inserted_kmers = h.occurrences;
+  s.unique_kmers = h.unique;
+  s.filtered_singletons = c->cfg.use_filter ? (h.filter_new > h.unique ? h.filter_new - h.unique : 0) : 0;
+  s.ge2_kmers = h.ge2;
+  s.final_kmers = h.n_final;
+  s.purged_kmers = h.unique - h.n_final;
+  s.sum_counts = h.sum_counts;
+  s.max_count = h.max_count;
+  s.dropped = 0;
+  s.table_slots = c->table_slots;
+  s.table_bytes = c->table_slots * (32 + 8 * (uint64_t)(c->N - 1));
+  s.filter_bytes = c->filter_buckets * 32;
+  s.avg_kmer_count = h.n_final ? (double)h.sum_counts / (double)h.n_final : 0.0;
+  s.kernel_launches = c->launches;
+}
+
+extern "C" int kc_finalize(kc_ctx *c, kc_stats *stats) {
+  if (!c) return KC_ERR_ARG;
+  if (c->phase != PH_INSERTED) return fail(c, KC_ERR_STATE, "kc_finalize: call kc_insert first");
+  CK(cudaSetDevice(c->device));
+  CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+  c->stats.ms_insert = ms;
+  if (c->h_ctr.err_table_full) {
+    fill_stats(c);
+    return fail(c, KC_ERR_TABLE_FULL, "k-mer table full (%llu slots, %llu keys placed): results undefined, enlarge table_slots",
+                (unsigned long long)c->table_slots, (unsigned long long)c->h_ctr.unique);
+  }
+  if (c->h_ctr.err_ovf_full) return fail(c, KC_ERR_TABLE_FULL, "saturation side table full");
+  const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
+  int rc = alloc_results(c, c->res_final, c->h_ctr.ge2, false);
+  if (rc) return rc;
+  if (keep_ext && (rc = alloc_results(c, c->res_ext, c->h_ctr.ge2, true))) return rc;
+
+  FinalizeParams fp;
+  memset(&fp, 0, sizeof fp);
+  fp.k = c->k;
+  fp.n_words = c->N;
+  fp.dmin_thres = c->cfg.dmin_thres;
+  fp.keep_ext = keep_ext;
+  fp.dyn_min_depth = c->cfg.dyn_min_depth;
+  fp.n_slots = c->table_slots;
+  fp.A = c->d_A;
+  fp.B = c->d_B;
+  fp.ovf = c->ovf;
+  fp.ctr = c->d_ctr;
+  fp.out_keys = c->res_final.keys;
+  fp.out_counts = c->res_final.counts;
+  fp.out_left = c->res_final.left;
+  fp.out_right = c->res_final.right;
+  fp.cap_final = c->res_final.cap;
+  fp.ext_keys = c->res_ext.keys;
+  fp.ext_counts = c->res_ext.counts;
+  fp.ext_ext8 = c->res_ext.ext8;
+  fp.ext_left = c->res_ext.left;
+  fp.ext_right = c->res_ext.right;
+  fp.cap_ext = c->res_ext.cap;
+  CK(cudaEventRecord(c->ev0, c->stream));
+  CK(launch_finalize(fp, c->sm_count, c->stream, &c->launches));
+  CK(cudaEventRecord(c->ev1, c->stream));
+  CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+  c->stats.ms_finalize = ms;
+  c->res_final.n = c->h_ctr.n_final;
+  c->res_ext.n = keep_ext ? c->h_ctr.n_ext : 0;
+  if (c->res_final.n > c->res_final.cap || c->res_ext.n > c->res_ext.cap) return fail(c, KC_ERR_STATE, "finalize: result overflow");
+  fill_stats(c);
+  c->phase = PH_FINALIZED;
+  if (stats) *stats = c->stats;
+  return KC_OK;
+}
+
+extern "C" int kc_get_stats(kc_ctx *c, kc_stats *stats) {
+  if (!c || !stats) return KC_ERR_ARG;
+  c->stats.kernel_launches = c->launches;
+  *stats = c->stats;
+  return KC_OK;
+}
+
+extern "C" int kc_reset(kc_ctx *c) {
+  if (!c) return KC_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->stream));
+  free_results(c->res_final);
+  free_results(c->res_ext);
+  c->phase = PH_EMPTY;
+  c->caps_valid = false;  // the next kc_parse samples the reads again, as a fresh stage would
+  c->recv_off.clear();
+  return KC_OK;
+}
+
+extern "C" int kc_run(kc_ctx *c, kc_stats *stats) {
+  if (!c) return KC_ERR_ARG;
+  if (c->G != 1) return fail(c, KC_ERR_ARG, "kc_run: single-rank only; multi-rank callers drive kc_parse / kc_exchange_* / kc_insert / kc_finalize");
+  int rc = kc_parse(c);
+  if (rc) return rc;
+  for (int attempt = 0; attempt < 4; attempt++) {
+    rc = kc_insert(c);
+    if (rc) return rc;
+    rc = kc_finalize(c, stats);
+    if (rc != KC_ERR_TABLE_FULL || c->cfg.table_slots) return rc;
+    c->table_slots *= 2;  // automatic sizing under-estimated: grow and insert again from the resident supermers
+    c->phase = PH_PARSED;
+  }
+  return rc;
+}
+
+// ------------------------------------------------------------------------------------------------ results
+static ResultSet *pick(kc_ctx *c, int extended) {
+  if (!c || c->phase != PH_FINALIZED) return nullptr;
+  if (extended && !(c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS)) return nullptr;
+  return extended ? &c->res_ext : &c->res_final;
+}
+
+extern "C" int kc_result_size(kc_ctx *c, int extended, uint64_t *n) {
+  ResultSet *r = pick(c, extended);
+  if (!r || !n) return fail(c, KC_ERR_STATE, "no %s result (finalize first%s)", extended ? "extended" : "final",
+                            extended ? ", with KC_FLAG_KEEP_EXT_COUNTS" : "");
+  *n = r->n;
+  return KC_OK;
+}
+
+struct HostResult {
+  std::vector<uint64_t> keys;
+  std::vector<uint16_t> counts, ext8;
+  std::vector<char> left, right;
+};
+
+static int fetch(kc_ctx *c, ResultSet *r, HostResult &h, bool want_ext) {
+  h.keys.resize(r->n * c->N);
+  h.counts.resize(r->n);
+  h.left.resize(r->n);
+  h.right.resize(r->n);
+  CK(cudaMemcpyAsync(h.keys.data(), r->keys, r->n * c->N * 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(h.counts.data(), r->counts, r->n * 2, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(h.left.data(), r->left, r->n, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(h.right.data(), r->right, r->n, cudaMemcpyDeviceToHost, c->stream));
+  if (want_ext && r->ext8) {
+    h.ext8.resize(r->n * 8);
+    CK(cudaMemcpyAsync(h.ext8.data(), r->ext8, r->n * 16, cudaMemcpyDeviceToHost, c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  return KC_OK;
+}
+
+// Sorting is not on the hot path (only dumps and tests need an order): permutation on the host, applied and written back.
+extern "C" int kc_result_sort(kc_ctx *c, int extended) {
+  ResultSet *r = pick(c, extended);
+  if (!r) return fail(c, KC_ERR_STATE, "kc_result_sort: no result");
+  if (r->sorted || r->n == 0) {
+    r->sorted = true;
+    return KC_OK;
+  }
+  CK(cudaSetDevice(c->device));
+  HostResult h;
+  int rc = fetch(c, r, h, true);
+  if (rc) return rc;
+  const int N = c->N;
+  std::vector<uint64_t> order(r->n);
+  std::iota(order.begin(), order.end(), 0);
+  std::sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b) {
+    return std::lexicographical_compare(&h.keys[a * N], &h.keys[a * N] + N, &h.keys[b * N], &h.keys[b * N] + N);
+  });
+  HostResult s;
+  s.keys.resize(h.keys.size());
+  s.counts.resize(r->n);
+  s.left.resize(r->n);
+  s.right.resize(r->n);
+  s.ext8.resize(h.ext8.size());
+  for (uint64_t i = 0; i < r->n; i++) {
+    uint64_t o = order[i];
+    for (int j = 0; j < N; j++) s.keys[i * N + j] = h.keys[o * N + j];
+    s.counts[i] = h.counts[o];
+    s.left[i] = h.left[o];
+    s.right[i] = h.right[o];
+    if (!h.ext8.empty())
+      for (int f = 0; f < 8; f++) s.ext8[i * 8 + f] = h.ext8[o * 8 + f];
+  }
+  CK(cudaMemcpyAsync(r->keys, s.keys.data(), r->n * N * 8, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(r->counts, s.counts.data(), r->n * 2, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(r->left, s.left.data(), r->n, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(r->right, s.right.data(), r->n, cudaMemcpyHostToDevice, c->stream));
+  if (!s.ext8.empty()) CK(cudaMemcpyAsync(r->ext8, s.ext8.data(), r->n * 16, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  r->sorted = true;
+  return KC_OK;
+}
+
+extern "C" int kc_result_copy(kc_ctx *c, int extended, uint64_t *keys, uint16_t *counts, char *left, char *right, uint16_t *ext8) {
+  ResultSet *r = pick(c, extended);
+  if (!r) return fail(c, KC_ERR_STATE, "kc_result_copy: no result");
+  CK(cudaSetDevice(c->device));
+  if (keys) CK(cudaMemcpyAsync(keys, r->keys, r->n * c->N * 8, cudaMemcpyDeviceToHost, c->stream));
+  if (counts) CK(cudaMemcpyAsync(counts, r->counts, r->n * 2, cudaMemcpyDeviceToHost, c->stream));
+  if (left) CK(cudaMemcpyAsync(left, r->left, r->n, cudaMemcpyDeviceToHost, c->stream));
+  if (right) CK(cudaMemcpyAsync(right, r->right, r->n, cudaMemcpyDeviceToHost, c->stream));
+  if (ext8) {
+    if (!r->ext8) return fail(c, KC_ERR_ARG, "kc_result_copy: ext8 only exists for the extended result");
+    CK(cudaMemcpyAsync(ext8, r->ext8, r->n * 16, cudaMemcpyDeviceToHost, c->stream));
+  }
+  CK(cudaStreamSynchronize(c->stream));
+  return KC_OK;
+}
+
+extern "C" int kc_result_device_ptrs(kc_ctx *c, int extended, const uint64_t **keys, const uint16_t **counts, const char **left,
+                                     const char **right, const uint16_t **ext8) {
+  ResultSet *r = pick(c, extended);
+  if (!r) return fail(c, KC_ERR_STATE, "kc_result_device_ptrs: no result");
+  if (keys) *keys = r->keys;
+  if (counts) *counts = r->counts;
+  if (left) *left = r->left;
+  if (right) *right = r->right;
+  if (ext8) *ext8 = r->ext8;
+  return KC_OK;
+}
+
+extern "C" int kc_result_checksum(kc_ctx *c, int extended, uint64_t *checksum) {
+  ResultSet *r = pick(c, extended);
+  if (!r || !checksum) return fail(c, KC_ERR_STATE, "kc_result_checksum: no result");
+  CK(cudaSetDevice(c->device));
+  unsigned long long *d = nullptr;
+  CK(dev_alloc(&d, 1));
+  CK(cudaMemsetAsync(d, 0, 8, c->stream));
+  if (r->n) CK(launch_checksum(r->keys, r->counts, r->left, r->right, extended ? r->ext8 : nullptr, r->n, c->N, d, c->stream, &c->launches));
+  unsigned long long h = 0;
+  CK(cudaMemcpyAsync(&h, d, 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  cudaFree(d);
+  *checksum = h;
+  return KC_OK;
+}
+
+static void key_to_string(const uint64_t *w, int k, char *s) {
+  for (int i = 0; i < k; i++) s[i] = "ACGT"[(w[i / 32] >> (2 * (31 - (i % 32)))) & 3];
+  s[k] = 0;
+}
+
+extern "C" int kc_dump_sorted(kc_ctx *c, const char *path, int extended) {
+  ResultSet *r = pick(c, extended);
+  if (!r || !path) return fail(c, KC_ERR_STATE, "kc_dump_sorted: no result");
+  int rc = kc_result_sort(c, extended);
+  if (rc) return rc;
+  HostResult h;
+  rc = fetch(c, r, h, true);
+  if (rc) return rc;
+  FILE *f = fopen(path, "w");
+  if (!f) return fail(c, KC_ERR_IO, "cannot open %s", path);
+  char s[KC_MAX_K + 1];
+  for (uint64_t i = 0; i < r->n; i++) {
+    key_to_string(&h.keys[i * c->N], c->k, s);
+    if (extended && !h.ext8.empty()) {
+      const uint16_t *e = &h.ext8[i * 8];
+      fprintf(f, "%s %u %c %c %u %u %u %u %u %u %u %u\n", s, h.counts[i], h.left[i], h.right[i], e[0], e[1], e[2], e[3], e[4], e[5], e[6], e[7]);
+    } else {
+      fprintf(f, "%s %u %c %c\n", s, h.counts[i], h.left[i], h.right[i]);  // kmer_dht.cpp:286
+    }
+  }
+  fclose(f);
+  return KC_OK;
+}
+
+// host-side binary search in the sorted final result; see DESIGN.md "next" for the device-resident index
+extern "C" int kc_lookup(kc_ctx *c, const uint64_t *keys, uint64_t n, uint16_t *counts, char *left, char *right) {
+  ResultSet *r = pick(c, 0);
+  if (!r || (n && !keys)) return fail(c, KC_ERR_STATE, "kc_lookup: no result");
+  int rc = kc_result_sort(c, 0);
+  if (rc) return rc;
+  HostResult h;
+  rc = fetch(c, r, h, false);
+  if (rc) return rc;
+  const int N = c->N;
+  for (uint64_t i = 0; i < n; i++) {
+    const uint64_t *q = keys + i * N;
+    uint64_t lo = 0, hi = r->n;
+    while (lo < hi) {
+      uint64_t mid = (lo + hi) / 2;
+      if (std::lexicographical_compare(&h.keys[mid * N], &h.keys[mid * N] + N, q, q + N)) lo = mid + 1; else hi = mid;
+    }
+    bool hit = lo < r->n && std::equal(q, q + N, &h.keys[lo * N]);
+    if (counts) counts[i] = hit ? h.counts[lo] : 0;
+    if (left) left[i] = hit ? h.left[lo] : 0;
+    if (right) right[i] = hit ? h.right[lo] : 0;
+  }
+  return KC_OK;
+}
+
+// KmerDHT::get_kmer_target_rank (src/kcount/kmer_dht.cpp:193-196): greatest least-complement m-mer, quick_hash, % ranks
+extern "C" int kc_owner_of(const kc_ctx *c, const uint64_t *w) {
+  if (!c || !w) return KC_ERR_ARG;
+  const int k = c->k, m = c->m;
+  const uint64_t mask = m < 32 ? ((1ULL << (2 * m)) - 1) : ~0ULL;
+  uint64_t f = 0, r = 0, best = 0;
+  for (int i = 0; i < k; i++) {
+    uint64_t b = (w[i / 32] >> (2 * (31 - (i % 32)))) & 3;
+    f = ((f << 2) | b) & mask;
+    r = (r >> 2) | ((3 - b) << (2 * (m - 1)));
+    if (i >= m - 1) best = std::max(best, std::min(f, r));
+  }
+  return (int)(quick_hash(best << (64 - 2 * m)) % (uint64_t)c->G);
+}

@@ -1,0 +1,140 @@
+// kc_internal.h -- structures shared between the kernels (kc_parse.cu, kc_insert.cu, kc_finalize.cu) and the
+// C ABI / context code (kc_api.cu). Not installed; the public surface is include/kcount_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "kc_device.cuh"
+
+namespace kc {
+
+// ---- hash table ---------------------------------------------------------------
+// One 32-byte, sector-aligned block per slot holds everything an insert touches after the key compare:
+//   N == 1 : key0x = ~key (0 = empty), claimed with one 64-bit CAS; tag unused
+//   N >= 2 : key0x = key word 0; tag = 0 empty / 1 being written / (hash fingerprint | 2) published;
+//            key words 1..N-1 live in the side array keyB[(N-1) * slot]
+// left/right pack four saturating 16-bit counters (A,C,G,T at bits 0,16,32,48); count is 32-bit and is
+// kept from running past 65535 + (occurrences in flight) -- see add_counts() in kc_insert.cu.
+struct alignas(32) SlotA {
+  uint64_t key0x;
+  uint32_t count;
+  uint32_t tag;
+  uint64_t left;
+  uint64_t right;
+};
+static_assert(sizeof(SlotA) == 32, "slot block must be one 32-byte sector");
+
+// extension increments that arrive after a k-mer's count reached 65535 go to this small side table so
+// that the packed 16-bit fields can never carry into each other (exact u16 saturation, kcount_cpu.cpp:147-164)
+struct Overflow {
+  uint64_t *keys;  // slot index + 1, 0 = empty
+  uint32_t *ext;   // 8 counters per entry
+  uint64_t mask;   // capacity - 1
+};
+
+struct Region {  // table / filter range owned by one local bin
+  uint64_t slot_base, n_slots;
+  uint64_t bucket_base, n_buckets;
+};
+
+struct Segment {  // run of supermer records of one (source rank, local bin)
+  const uint8_t *ptr;
+  uint32_t n_records;
+  uint32_t bin;
+};
+
+enum InsertMode { MODE_INSERT = 0, MODE_ADMIT = 1, MODE_UPDATE = 2 };
+
+struct DevCounters {  // device-resident, zeroed by kc_reset
+  unsigned long long tile_cursor;
+  unsigned long long unique;        // keys that claimed a table slot
+  unsigned long long ge2;           // keys whose count reached 2
+  unsigned long long occurrences;   // k-mer occurrences inserted
+  unsigned long long records_in;    // non-empty supermer records consumed
+  unsigned long long filter_new;    // first sightings registered by the filter
+  unsigned long long n_final, n_ext;  // finalize output cursors
+  unsigned long long sum_counts, max_count;
+  unsigned long long purged;
+  unsigned int err_table_full, err_ovf_full;
+  unsigned long long parse_counted, parse_records, parse_raw;
+  unsigned int err_bins_full;
+};
+
+struct InsertParams {
+  int k, rec_bytes, n_segments;
+  const Segment *segments;
+  const uint32_t *seg_tile_start;  // [n_segments + 1] exclusive prefix of tiles
+  const Region *regions;
+  SlotA *A;
+  uint64_t *B;
+  uint32_t *filter;  // 8 u32 words (16 tags) per bucket
+  Overflow ovf;
+  DevCounters *ctr;
+};
+
+struct FinalizeParams {
+  int k, n_words, dmin_thres, keep_ext;
+  double dyn_min_depth;
+  uint64_t n_slots;
+  const SlotA *A;
+  const uint64_t *B;
+  Overflow ovf;
+  DevCounters *ctr;
+  // survivors (D1)
+  uint64_t *out_keys;
+  uint16_t *out_counts;
+  char *out_left, *out_right;
+  uint64_t cap_final;
+  // all entries with count >= 2 (D2), only when keep_ext
+  uint64_t *ext_keys;
+  uint16_t *ext_counts, *ext_ext8;
+  char *ext_left, *ext_right;
+  uint64_t cap_ext;
+};
+
+struct ParseParams {
+  const uint8_t *bytes;
+  const uint64_t *offsets;
+  const uint16_t *lens;
+  uint64_t n_reads;
+  uint32_t read_stride;  // 1 = all reads, S = every S-th read (capacity sampling pass)
+  int count_only;
+  int k, m, qual_cutoff, rec_bytes;
+  uint32_t n_ids;        // n_ranks * local_bins
+  uint32_t bins_mask;    // local_bins - 1
+  FastDiv div_ranks;
+  uint8_t *bins;                     // record storage
+  const uint64_t *bin_base;          // [n_ids] first record of each bin
+  const uint64_t *bin_cap;           // [n_ids] capacity in records
+  unsigned long long *bin_cursor;    // [n_ids] records appended (may run past cap: then nothing is written)
+  DevCounters *ctr;
+};
+
+// ---- launchers (each returns the cudaError of the launch) ---------------------------------------------
+cudaError_t launch_parse(const ParseParams &p, int sm_count, cudaStream_t s, uint64_t *launches);
+// writes empty-record headers over [cursor, cap) of every bin so the whole bin range can be shipped/read
+cudaError_t launch_seal_bins(uint8_t *bins, const uint64_t *bin_base, const uint64_t *bin_cap, const unsigned long long *bin_cursor,
+                             uint32_t n_ids, int rec_bytes, cudaStream_t s, uint64_t *launches);
+// per-destination header blocks + segment/region tables for the insert kernel
+struct PlanParams {
+  int n_src, local_bins, rec_bytes, tile_records;
+  // per source: pointer to its region for this rank = [header: local_bins x {u32 first_record, u32 n_records}][records]
+  const uint8_t *const *src_ptr;
+  Segment *segments;         // [local_bins * n_src], bin-major
+  uint32_t *seg_tile_start;  // [local_bins * n_src + 1]
+  Region *regions;           // [local_bins]
+  uint64_t table_slots, filter_buckets;
+  unsigned long long *total_records;  // out
+};
+cudaError_t launch_plan(const PlanParams &p, cudaStream_t s, uint64_t *launches);
+cudaError_t launch_write_headers(uint8_t *const *dst_header, const uint64_t *bin_base, const unsigned long long *bin_cursor,
+                                 const uint64_t *bin_cap, int n_ranks, int local_bins, cudaStream_t s, uint64_t *launches);
+cudaError_t launch_insert(const InsertParams &p, int n_words, int mode, bool dedup, int sm_count, cudaStream_t s, uint64_t *launches);
+cudaError_t launch_finalize(const FinalizeParams &p, int sm_count, cudaStream_t s, uint64_t *launches);
+cudaError_t launch_checksum(const uint64_t *keys, const uint16_t *counts, const char *left, const char *right, const uint16_t *ext8,
+                            uint64_t n, int n_words, unsigned long long *out, cudaStream_t s, uint64_t *launches);
+
+static const int kTileRecords = 256;  // supermer records staged in shared memory per insert tile
+static const int kHeaderAlign = 64;
+
+}  // namespace kc

@@ -1,0 +1,105 @@
+"""Owner exchange of supermer records: the replacement for the reference's UPC++ aggregated RPCs
+(KmerDHT::add_supermer / flush_updates, src/kcount/kmer_dht.cpp:248-258; ThreeTierAggrStore, source absent).
+
+One process per GPU. After the parse phase every rank holds, per destination owner, one contiguous device buffer
+([bin header][records]); sizes are exchanged first, then one all-to-all moves the buffers HBM -> HBM over NVLink
+(NCCL). The stage object only has to offer send_sizes()/send_ptr()/recv_buffer()/exchange_done(), so the same driver
+runs against the CUDA stage (nccl) and against a CPU stand-in in the gloo tests.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+class _DevBytes:
+    """Zero-copy torch view of raw device memory (no ownership)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+def device_bytes(ptr, nbytes, device):
+    if nbytes == 0:
+        return torch.empty(0, dtype=torch.uint8, device=device)
+    return torch.as_tensor(_DevBytes(ptr, nbytes), device=device)
+
+
+def _is_cuda_stage(stage):
+    return hasattr(stage, "L")  # KcountStage (C ABI) as opposed to a host stand-in used by the CPU tests
+
+
+def exchange_sizes(send_sizes, group=None, device="cpu"):
+    """all-to-all of one u64 per pair: recv[s] = what rank s will send me."""
+    world = dist.get_world_size(group)
+    t_send = torch.as_tensor(np.asarray(send_sizes, np.int64), device=device)
+    t_recv = torch.empty(world, dtype=torch.int64, device=device)
+    dist.all_to_all_single(t_recv, t_send, group=group)
+    return t_recv.cpu().numpy().astype(np.uint64)
+
+
+def exchange_supermers(stage, group=None):
+    """Move every rank's per-owner supermer buffers to their owners. Returns (bytes_sent, bytes_received, seconds)
+    where seconds is the device time of the data all-to-all (CUDA events) on NCCL, wall time on gloo."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    assert world == stage.n_ranks and rank == stage.rank
+    cuda = _is_cuda_stage(stage)
+    dev = torch.device("cuda", torch.cuda.current_device()) if cuda else torch.device("cpu")
+    send_sizes = np.asarray(stage.send_sizes(), np.uint64)
+    send_sizes[rank] = 0
+    recv_sizes = exchange_sizes(send_sizes, group, dev)
+    recv_sizes[rank] = 0
+    recv_ptr, recv_off = stage.recv_buffer(recv_sizes)
+    if cuda:
+        stage.sync()
+        sends = [device_bytes(stage.send_ptr(d), int(send_sizes[d]), dev) for d in range(world)]
+        recvs = [device_bytes(recv_ptr + int(recv_off[s]), int(recv_sizes[s]), dev) for s in range(world)]
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        dist.all_to_all(recvs, sends, group=group)
+        e1.record()
+        torch.cuda.synchronize()
+        secs = e0.elapsed_time(e1) / 1e3
+    else:
+        import time
+
+        sends = [stage.send_view(d) for d in range(world)]
+        recvs = [stage.recv_view(s) for s in range(world)]
+        t0 = time.perf_counter()
+        dist.all_to_all(recvs, sends, group=group)
+        secs = time.perf_counter() - t0
+    stage.exchange_done()
+    return int(send_sizes.sum()), int(recv_sizes.sum()), secs
+
+
+def global_avg_kmer_count(stats, group=None):
+    """avg depth over all ranks = sum(count) / number of k-mers (kcount_cpu.cpp:586-596, reduce_all)."""
+    backend = dist.get_backend(group)
+    dev = "cuda" if backend == "nccl" else "cpu"
+    t = torch.tensor([float(stats["sum_counts"]), float(stats["final_kmers"])], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, group=group)
+    return float(t[0] / t[1]) if t[1] > 0 else 0.0
+
+
+def reduce_stats(stats, group=None):
+    """Sum the per-rank counters the reference reduces (kcount_gpu.cpp:294-364); max for max_count / times."""
+    backend = dist.get_backend(group)
+    dev = "cuda" if backend == "nccl" else "cpu"
+    sum_keys = ["n_reads", "n_bases", "raw_kmers", "counted_kmers", "supermers_out", "supermer_bytes_out", "supermers_in",
+                "inserted_kmers", "unique_kmers", "ge2_kmers", "final_kmers", "purged_kmers", "sum_counts", "table_bytes"]
+    max_keys = ["max_count", "ms_parse", "ms_insert", "ms_finalize"]
+    s = torch.tensor([float(stats[k]) for k in sum_keys], dtype=torch.float64, device=dev)
+    m = torch.tensor([float(stats[k]) for k in max_keys], dtype=torch.float64, device=dev)
+    dist.all_reduce(s, group=group)
+    dist.all_reduce(m, op=dist.ReduceOp.MAX, group=group)
+    out = {k: int(v) for k, v in zip(sum_keys, s.tolist())}
+    out.update({k: v for k, v in zip(max_keys, m.tolist())})
+    out["max_count"] = int(out["max_count"])
+    out["avg_kmer_count"] = out["sum_counts"] / out["final_kmers"] if out["final_kmers"] else 0.0
+    # load balance of the owners, as the reference logs it (kcount.cpp:97-100)
+    mine = torch.tensor([float(stats["inserted_kmers"])], dtype=torch.float64, device=dev)
+    mx = mine.clone()
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
+    world = dist.get_world_size(group)
+    out["owner_imbalance"] = float(mx.item() * world / max(out["inserted_kmers"], 1))
+    return out

@@ -1,0 +1,138 @@
+"""Seeded synthetic PackedRead streams (kc_synth_* of the C ABI) and the configs of BASELINE.md section 4."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _lib
+
+
+class ReadSet:
+    """Reads in the reference's in-memory encoding (src/packed_reads.cpp:99-126): one byte per base =
+    base(A0 C1 G2 T3 N4) | min(qual - offset, 31) << 3, plus offsets[] / lens[] (the 16-byte PackedRead headers)."""
+
+    def __init__(self, bytes_, offsets, lens):
+        self.bytes = np.ascontiguousarray(bytes_, np.uint8)
+        self.offsets = np.ascontiguousarray(offsets, np.uint64)
+        self.lens = np.ascontiguousarray(lens, np.uint16)
+
+    def __len__(self):
+        return len(self.lens)
+
+    @property
+    def n_bases(self):
+        return int(self.lens.astype(np.uint64).sum())
+
+    def counted_kmers(self, k):
+        """sum over reads of max(0, len - k - 1): the unit of the headline metric (kcount_cpu.cpp:84-101)."""
+        l = self.lens.astype(np.int64)
+        return int(np.maximum(l - k - 1, 0).sum())
+
+    def slice(self, lo, hi):
+        off = self.offsets[lo:hi]
+        if len(off) == 0:
+            return ReadSet(np.zeros(0, np.uint8), off, self.lens[lo:hi])
+        b0 = int(off[0])
+        b1 = int(self.offsets[hi - 1]) + int(self.lens[hi - 1])
+        return ReadSet(self.bytes[b0:b1], off - np.uint64(b0), self.lens[lo:hi])
+
+    def save(self, path):
+        L = _lib.lib()
+        rc = L.kc_reads_save(os.fsencode(path), self.bytes.ctypes.data, len(self.bytes), self.offsets.ctypes.data,
+                             self.lens.ctypes.data, len(self.lens))
+        if rc:
+            raise _lib.KcError(rc, f"kc_reads_save({path})")
+
+    @staticmethod
+    def from_strings(seqs, quals=None, qual_offset=33):
+        """Build a ReadSet from ACGTN strings (+ optional quality strings), as PackedRead's constructor does."""
+        code = {c: i for i, c in enumerate("ACGT")}
+        bs, offs, lens, at = [], [], [], 0
+        for i, s in enumerate(seqs):
+            q = quals[i] if quals is not None else "I" * len(s)
+            assert len(q) == len(s)
+            for ch, qc in zip(s.upper(), q):
+                bs.append(code.get(ch, 4) | (min(ord(qc) - qual_offset, 31) << 3))
+            offs.append(at)
+            lens.append(len(s))
+            at += len(s)
+        return ReadSet(np.array(bs, np.uint8), np.array(offs, np.uint64), np.array(lens, np.uint16))
+
+    @staticmethod
+    def concat(sets):
+        bs = np.concatenate([s.bytes for s in sets])
+        lens = np.concatenate([s.lens for s in sets])
+        base, offs = 0, []
+        for s in sets:
+            offs.append(s.offsets + np.uint64(base))
+            base += len(s.bytes)
+        return ReadSet(bs, np.concatenate(offs), lens)
+
+
+def synth_config(**kw):
+    cfg = _lib.KcSynthConfig()
+    _lib.lib().kc_synth_config_default(C.byref(cfg))
+    for k, v in kw.items():
+        if not hasattr(cfg, k):
+            raise TypeError(f"unknown synth option {k}")
+        setattr(cfg, k, v)
+    return cfg
+
+
+# BASELINE.md section 4 (n_reads is the config's full size; callers may take a prefix of the stream)
+CONFIGS = {
+    "C1": dict(synth=dict(seed=1001, n_genomes=1, genome_len_min=5_000_000, genome_len_max=5_000_000, sub_rate=0.005),
+               n_reads=1_000_000, k=(21,)),
+    "C2": dict(synth=dict(seed=2002, n_genomes=100, genome_len_min=1_000_000, genome_len_max=5_000_000, abundance_sigma=1.0,
+                          sub_rate=0.005), n_reads=20_000_000, k=(33,)),
+    "C3": dict(synth=dict(seed=3003, n_genomes=100, genome_len_min=1_000_000, genome_len_max=5_000_000, abundance_sigma=1.0,
+                          sub_rate=0.005, paired=1, insert_mean=300.0, insert_sd=30.0), n_reads=200_000_000, k=(21, 33, 55)),
+    "C4": dict(synth=dict(seed=2002, n_genomes=100, genome_len_min=1_000_000, genome_len_max=5_000_000, abundance_sigma=1.0,
+                          sub_rate=0.005), n_reads=20_000_000, k=(77, 99)),
+    "C5": dict(synth=dict(seed=5005, n_genomes=100, genome_len_min=1_000_000, genome_len_max=5_000_000, abundance_sigma=1.0,
+                          sub_rate=0.01), n_reads=20_000_000, k=(21, 33)),
+}
+
+
+class Synth:
+    """Handle on a seeded read stream; read i depends only on (seed, i)."""
+
+    def __init__(self, cfg=None, **kw):
+        self.L = _lib.lib()
+        self.cfg = cfg if cfg is not None else synth_config(**kw)
+        self.h = C.c_void_p()
+        rc = self.L.kc_synth_create(C.byref(self.cfg), C.byref(self.h))
+        if rc:
+            raise _lib.KcError(rc, "kc_synth_create")
+
+    def close(self):
+        if self.h:
+            self.L.kc_synth_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def generate(self, first, n, n_threads=0, out_bytes=None):
+        n_threads = n_threads or min(32, os.cpu_count() or 1)
+        cap = n * self.cfg.read_len
+        b = out_bytes if out_bytes is not None else np.empty(cap, np.uint8)
+        assert len(b) >= cap
+        off = np.empty(n, np.uint64)
+        ln = np.empty(n, np.uint16)
+        nb = C.c_uint64()
+        rc = self.L.kc_synth_generate(self.h, first, n, b.ctypes.data, off.ctypes.data, ln.ctypes.data, C.byref(nb), n_threads)
+        if rc:
+            raise _lib.KcError(rc, "kc_synth_generate")
+        return ReadSet(b[: nb.value], off, ln)
+
+
+def generate(config="C1", n_reads=None, first=0, **overrides):
+    """Reads [first, first + n_reads) of a named BASELINE config (or of explicit kc_synth options)."""
+    spec = dict(CONFIGS[config]["synth"]) if config in CONFIGS else {}
+    spec.update(overrides)
+    s = Synth(**spec)
+    try:
+        n = n_reads if n_reads is not None else CONFIGS[config]["n_reads"]
+        return s.generate(first, n)
+    finally:
+        s.close()

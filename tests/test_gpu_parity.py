@@ -1,0 +1,72 @@
+"""GPU parity: the CUDA stage (through the C ABI) against the CPU oracle on the same seeded reads. Bit-exact:
+sorted survivors (dump D1) and all entries with count >= 2 incl. the 8 extension counters and X/F (dump D2)."""
+import numpy as np
+import pytest
+
+import mhm2_kmer_analysis_v2_b200 as K
+from util import assert_same, gpu_multi, gpu_single, merge_results, oracle_run
+
+pytestmark = pytest.mark.gpu
+
+SMALL = dict(n_genomes=3, genome_len_min=30_000, genome_len_max=60_000, abundance_sigma=1.0, sub_rate=0.005)
+
+
+@pytest.mark.parametrize("k", [21, 33, 55, 77, 99])
+def test_single_gpu_matches_oracle(oracle_mod, k):
+    reads = K.generate(None, 12_000, seed=100 + k, **SMALL)
+    o = oracle_run(oracle_mod, reads, k)
+    st, stats = gpu_single(reads, k)
+    assert stats["counted_kmers"] == o.counted_kmers() == reads.counted_kmers(k)
+    assert stats["inserted_kmers"] == o.counted_kmers()
+    assert stats["unique_kmers"] == o.num_entries()
+    assert_same(st.result(True), o.result(True), f"k={k} D2")
+    assert_same(st.result(False), o.result(False), f"k={k} D1")
+    assert st.checksum(False) == o.checksum(False)
+    assert st.checksum(True) == o.checksum(True)
+    assert stats["final_kmers"] == len(o.result(False))
+    assert abs(stats["avg_kmer_count"] - o.avg_kmer_count()) < 1e-9
+    st.close()
+
+
+@pytest.mark.parametrize("k,G", [(21, 2), (21, 3), (33, 4), (55, 8), (77, 2), (99, 3)])
+def test_owner_partition_matches_oracle(oracle_mod, k, G):
+    """G emulated ranks: per-owner tables equal the oracle's per-rank tables; the union equals the 1-rank result."""
+    reads = K.generate(None, 8_000, seed=200 + k, **SMALL)
+    o = oracle_run(oracle_mod, reads, k, n_ranks=G)
+    stages, stats = gpu_multi(reads, k, G)
+    for r, st in enumerate(stages):
+        assert stats[r]["supermers_in"] >= 0
+        assert_same(st.result(True), o.result(True, rank=r), f"k={k} G={G} rank {r} D2")
+        assert_same(st.result(False), o.result(False, rank=r), f"k={k} G={G} rank {r} D1")
+    union = merge_results([st.result(True) for st in stages], stages[0].N)
+    assert_same(union, o.result(True), f"k={k} G={G} union")
+    assert sum(s["inserted_kmers"] for s in stats) == reads.counted_kmers(k)
+    for st in stages:
+        st.close()
+
+
+@pytest.mark.parametrize("k,bins,rec", [(21, 16, 16), (21, 64, 0), (33, 256, 32), (55, 8, 64), (21, 1, 16), (33, 1, 32)])
+def test_local_bins_and_record_sizes(oracle_mod, k, bins, rec):
+    reads = K.generate(None, 8_000, seed=300 + k, **SMALL)
+    o = oracle_run(oracle_mod, reads, k)
+    st, stats = gpu_single(reads, k, local_bins=bins, record_bytes=rec)
+    assert_same(st.result(True), o.result(True), f"k={k} bins={bins} rec={rec}")
+    st.close()
+
+
+@pytest.mark.parametrize("k", [21, 33, 77])
+def test_filter_on_equals_filter_off(oracle_mod, k):
+    reads = K.generate(None, 8_000, seed=400 + k, **SMALL)
+    o = oracle_run(oracle_mod, reads, k)
+    st, stats = gpu_single(reads, k, use_filter=True)
+    assert_same(st.result(True), o.result(True), f"k={k} filter on")
+    assert stats["unique_kmers"] < o.num_entries(), "the filter should keep most singletons out of the table"
+    st.close()
+
+
+def test_no_dedup_path(oracle_mod):
+    reads = K.generate(None, 6_000, seed=77, **SMALL)
+    o = oracle_run(oracle_mod, reads, 21)
+    st, _ = gpu_single(reads, 21, warp_dedup=False)
+    assert_same(st.result(True), o.result(True), "no dedup")
+    st.close()
