@@ -501,14 +501,15 @@ static uint64_t used_region_bytes(kc_ctx *c, int o) {
 
 extern "C" int kc_exchange_send_sizes(kc_ctx *c, uint64_t *send_bytes) {
   if (!c || !send_bytes) return KC_ERR_ARG;
-  if (c->phase != PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_send_sizes: call kc_parse first");
+  if (c->phase < PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_send_sizes: call kc_parse first");
   for (int o = 0; o < c->G; o++) send_bytes[o] = (o == c->rank) ? 0 : used_region_bytes(c, o);
   return KC_OK;
 }
 
 extern "C" int kc_exchange_send_ptr(kc_ctx *c, int dst, void **dev_ptr) {
   if (!c || !dev_ptr || dst < 0 || dst >= c->G) return KC_ERR_ARG;
-  if (c->phase != PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_send_ptr: call kc_parse first");
+  // the send buffers stay valid until kc_reset / kc_add_reads: peers may still be pulling after this rank moved on
+  if (c->phase < PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_send_ptr: call kc_parse first");
   *dev_ptr = c->d_bins + c->h_region_off[dst];
   return KC_OK;
 }
