@@ -111,6 +111,11 @@ typedef struct {
   double avg_kmer_count;       /* sum_counts / final_kmers, rank-local; kcount_cpu.cpp:594-596 */
   double ms_parse, ms_insert, ms_finalize; /* device time of the last run of each phase (CUDA events) */
   uint64_t kernel_launches;    /* kernels launched by this context so far */
+  /* device time (CUDA events on the context's stream) of the kernels alone, last run of each phase */
+  double ms_parse_kernel;      /* supermer kernel(s) over all read chunks, without the capacity-sampling pass */
+  double ms_insert_kernel;     /* insert kernel (both passes when the filter is on), without table clearing / planning */
+  double ms_table_clear;       /* zeroing of table, filter and side table before the insert */
+  uint64_t insert_kernel_launches; /* launches covered by ms_insert_kernel */
 } kc_stats;
 
 /* ---- lifecycle ---------------------------------------------------------------------------------- */
@@ -153,6 +158,10 @@ int kc_run(kc_ctx *ctx, kc_stats *stats);
 int kc_reset(kc_ctx *ctx);
 int kc_sync(kc_ctx *ctx);
 int kc_get_stats(kc_ctx *ctx, kc_stats *stats);
+/* Device-side stopwatch for callers (bench.py): kc_timer_mark records CUDA event `slot` (0..7) on the context's stream;
+ * kc_timer_elapsed_ms synchronises on event `to` and returns the device time between two marks. */
+int kc_timer_mark(kc_ctx *ctx, int slot);
+int kc_timer_elapsed_ms(kc_ctx *ctx, int from, int to, double *ms);
 
 /* ---- results ------------------------------------------------------------------------------------ */
 uint32_t kc_key_words(const kc_ctx *ctx); /* N_LONGS = ceil(k/32) */

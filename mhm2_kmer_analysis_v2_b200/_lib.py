@@ -35,7 +35,8 @@ class KcStats(C.Structure):
         "inserted_kmers", "unique_kmers", "filtered_singletons", "ge2_kmers", "final_kmers", "purged_kmers", "sum_counts",
         "max_count", "dropped", "table_slots", "table_bytes", "filter_bytes")] + [
         ("avg_kmer_count", C.c_double), ("ms_parse", C.c_double), ("ms_insert", C.c_double), ("ms_finalize", C.c_double),
-        ("kernel_launches", C.c_uint64)]
+        ("kernel_launches", C.c_uint64), ("ms_parse_kernel", C.c_double), ("ms_insert_kernel", C.c_double),
+        ("ms_table_clear", C.c_double), ("insert_kernel_launches", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -73,6 +74,8 @@ PROTOTYPES = {
     "kc_reset": (C.c_int, [vp]),
     "kc_sync": (C.c_int, [vp]),
     "kc_get_stats": (C.c_int, [vp, C.POINTER(KcStats)]),
+    "kc_timer_mark": (C.c_int, [vp, C.c_int]),
+    "kc_timer_elapsed_ms": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "kc_key_words": (C.c_uint32, [vp]),
     "kc_result_size": (C.c_int, [vp, C.c_int, C.POINTER(C.c_uint64)]),
     "kc_result_sort": (C.c_int, [vp, C.c_int]),

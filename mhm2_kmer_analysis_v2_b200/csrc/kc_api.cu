@@ -47,6 +47,8 @@ struct kc_ctx {
   int device = 0, sm_count = 148;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev_pk0 = nullptr, ev_pk1 = nullptr, ev_ik0 = nullptr, ev_ik1 = nullptr, ev_clr = nullptr;
+  cudaEvent_t ev_user[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   std::string err;
   Phase phase = PH_EMPTY;
 
@@ -218,6 +220,12 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
   cudaEventCreate(&c->ev0);
   cudaEventCreate(&c->ev1);
+  cudaEventCreate(&c->ev_pk0);
+  cudaEventCreate(&c->ev_pk1);
+  cudaEventCreate(&c->ev_ik0);
+  cudaEventCreate(&c->ev_ik1);
+  cudaEventCreate(&c->ev_clr);
+  for (auto &e2 : c->ev_user) cudaEventCreate(&e2);
   if ((e = dev_alloc(&c->d_ctr, 1)) != cudaSuccess) return bail(e, "cudaMalloc");
   cudaMemsetAsync(c->d_ctr, 0, sizeof(DevCounters), c->stream);
   c->header_bytes = ((c->P * 8 + kHeaderAlign - 1) / kHeaderAlign) * kHeaderAlign;
@@ -274,8 +282,10 @@ extern "C" void kc_destroy(kc_ctx *c) {
   dev_free(c->d_ctr);
   free_results(c->res_final);
   free_results(c->res_ext);
-  if (c->ev0) cudaEventDestroy(c->ev0);
-  if (c->ev1) cudaEventDestroy(c->ev1);
+  for (cudaEvent_t e : {c->ev0, c->ev1, c->ev_pk0, c->ev_pk1, c->ev_ik0, c->ev_ik1, c->ev_clr})
+    if (e) cudaEventDestroy(e);
+  for (auto &e : c->ev_user)
+    if (e) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -436,10 +446,12 @@ static int run_parse(kc_ctx *c) {
   const uint32_t n = c->n_ids;
   CK(cudaMemsetAsync(c->d_cursor, 0, n * sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(&c->d_ctr->parse_counted, 0, 3 * sizeof(unsigned long long) + sizeof(unsigned int), c->stream));
+  CK(cudaEventRecord(c->ev_pk0, c->stream));
   for (auto &ch : c->chunks) {
     ParseParams p = parse_params(c, ch, 1, 0);
     CK(launch_parse(p, c->sm_count, c->stream, &c->launches));
   }
+  CK(cudaEventRecord(c->ev_pk1, c->stream));
   CK(launch_write_headers(c->d_hdr_ptrs, c->d_bin_first, c->d_cursor, c->d_bin_cap, c->G, c->P, c->stream, &c->launches));
   c->h_cursor.assign(n, 0);
   CK(cudaMemcpyAsync(c->h_cursor.data(), c->d_cursor, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
@@ -476,6 +488,8 @@ extern "C" int kc_parse(kc_ctx *c) {
   float ms = 0;
   cudaEventElapsedTime(&ms, c->ev0, c->ev1);
   c->stats.ms_parse = ms;
+  cudaEventElapsedTime(&ms, c->ev_pk0, c->ev_pk1);
+  c->stats.ms_parse_kernel = ms;
   c->stats.n_reads = c->n_reads;
   c->stats.n_bases = c->n_bases;
   c->stats.raw_kmers = c->h_ctr.parse_raw;
@@ -661,6 +675,7 @@ extern "C" int kc_insert(kc_ctx *c) {
   pp.table_slots = c->table_slots;
   pp.filter_buckets = c->filter_buckets;
   pp.total_records = c->d_total_records;
+  CK(cudaEventRecord(c->ev_clr, c->stream));
   CK(launch_plan(pp, c->stream, &c->launches));
 
   InsertParams ip;
@@ -677,6 +692,8 @@ extern "C" int kc_insert(kc_ctx *c) {
   ip.ovf = c->ovf;
   ip.ctr = c->d_ctr;
   const bool dedup = !(c->cfg.flags & KC_FLAG_NO_WARP_DEDUP);
+  CK(cudaEventRecord(c->ev_ik0, c->stream));
+  c->stats.insert_kernel_launches = c->cfg.use_filter ? 2 : 1;
   if (!c->cfg.use_filter) {
     CK(launch_insert(ip, c->N, MODE_INSERT, dedup, c->sm_count, c->stream, &c->launches));
   } else {
@@ -685,6 +702,7 @@ extern "C" int kc_insert(kc_ctx *c) {
     CK(cudaMemsetAsync(&c->d_ctr->tile_cursor, 0, sizeof(unsigned long long), c->stream));
     CK(launch_insert(ip, c->N, MODE_UPDATE, dedup, c->sm_count, c->stream, &c->launches));
   }
+  CK(cudaEventRecord(c->ev_ik1, c->stream));
   CK(cudaEventRecord(c->ev1, c->stream));
   c->phase = PH_INSERTED;
   free_results(c->res_final);
@@ -733,6 +751,10 @@ extern "C" int kc_finalize(kc_ctx *c, kc_stats *stats) {
   float ms = 0;
   cudaEventElapsedTime(&ms, c->ev0, c->ev1);
   c->stats.ms_insert = ms;
+  cudaEventElapsedTime(&ms, c->ev_ik0, c->ev_ik1);
+  c->stats.ms_insert_kernel = ms;
+  cudaEventElapsedTime(&ms, c->ev0, c->ev_clr);
+  c->stats.ms_table_clear = ms;
   if (c->h_ctr.err_table_full) {
     fill_stats(c);
     return fail(c, KC_ERR_TABLE_FULL, "k-mer table full (%llu slots, %llu keys placed): results undefined, enlarge table_slots",
@@ -787,6 +809,23 @@ extern "C" int kc_get_stats(kc_ctx *c, kc_stats *stats) {
   if (!c || !stats) return KC_ERR_ARG;
   c->stats.kernel_launches = c->launches;
   *stats = c->stats;
+  return KC_OK;
+}
+
+extern "C" int kc_timer_mark(kc_ctx *c, int slot) {
+  if (!c || slot < 0 || slot >= 8) return KC_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  CK(cudaEventRecord(c->ev_user[slot], c->stream));
+  return KC_OK;
+}
+
+extern "C" int kc_timer_elapsed_ms(kc_ctx *c, int from, int to, double *ms) {
+  if (!c || !ms || from < 0 || from >= 8 || to < 0 || to >= 8) return KC_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  CK(cudaEventSynchronize(c->ev_user[to]));
+  float f = 0;
+  CK(cudaEventElapsedTime(&f, c->ev_user[from], c->ev_user[to]));
+  *ms = f;
   return KC_OK;
 }
 

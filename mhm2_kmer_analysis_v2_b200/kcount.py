@@ -110,6 +110,14 @@ class KcountStage:
         self._ck(self.L.kc_get_stats(self.h, C.byref(st)))
         return st.as_dict()
 
+    def timer_mark(self, slot):
+        self._ck(self.L.kc_timer_mark(self.h, slot))
+
+    def timer_elapsed_ms(self, a, b):
+        ms = C.c_double()
+        self._ck(self.L.kc_timer_elapsed_ms(self.h, a, b, C.byref(ms)))
+        return ms.value
+
     # ---- exchange (multi-rank)
     def send_sizes(self):
         a = np.zeros(self.n_ranks, np.uint64)

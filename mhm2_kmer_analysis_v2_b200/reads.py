@@ -69,6 +69,30 @@ class ReadSet:
         return ReadSet(bs, np.concatenate(offs), lens)
 
 
+class PinnedBuffer:
+    """Page-locked host memory from kc_host_alloc (cudaHostAlloc), viewed as a numpy u8 array."""
+
+    def __init__(self, nbytes):
+        self.L = _lib.lib()
+        self.ptr = C.c_void_p()
+        self.nbytes = max(int(nbytes), 1)
+        rc = self.L.kc_host_alloc(C.byref(self.ptr), self.nbytes)
+        if rc:
+            raise _lib.KcError(rc, f"kc_host_alloc({self.nbytes})")
+        self.array = np.ctypeslib.as_array(C.cast(self.ptr, C.POINTER(C.c_uint8)), shape=(self.nbytes,))
+
+    def view(self, dtype, count, offset=0):
+        return self.array[offset:offset + count * np.dtype(dtype).itemsize].view(dtype)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            self.L.kc_host_free(self.ptr)
+            self.ptr = None
+
+    __del__ = free
+
+
 def synth_config(**kw):
     cfg = _lib.KcSynthConfig()
     _lib.lib().kc_synth_config_default(C.byref(cfg))

@@ -248,7 +248,7 @@ int main(int argc, char **argv) {
   uint64_t n = a.max_reads && a.max_reads < rf.n_reads ? a.max_reads : rf.n_reads;
   // mailbox capacity: every k-mer of a shard could in the worst case travel as its own (k+2)-char supermer
   uint64_t shard_bytes = (rf.n_bytes * (double)n / std::max<uint64_t>(rf.n_reads, 1)) / P + 1;
-  uint64_t box_cap = std::max<uint64_t>(64ull << 20, shard_bytes * 12 / P * 2);
+  uint64_t box_cap = std::max<uint64_t>(4ull << 20, shard_bytes * 12 / P * 2);
   w.init_shared(P, box_cap);
   RankResult *res = (RankResult *)shim::World::shared_alloc(sizeof(RankResult) * P);
   std::vector<pid_t> pids;
