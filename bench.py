@@ -205,6 +205,7 @@ def main():
     ap.add_argument("--filter", type=int, default=0, help="1 = two-choice singleton filter on")
     ap.add_argument("--local-bins", type=int, default=0)
     ap.add_argument("--record-bytes", type=int, default=0)
+    ap.add_argument("--table-slots", type=int, default=0, help="exact table size in slots (0 = the reference's sizing rule)")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-sample-reads", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -258,7 +259,7 @@ def main():
     h2d_bytes = len(reads.bytes) + n * 10
 
     st = K.KcountStage(k, rank=rank, n_ranks=world, device=local_rank, est_kmers=raw_local, use_filter=bool(args.filter),
-                       local_bins=args.local_bins, record_bytes=args.record_bytes)
+                       local_bins=args.local_bins, record_bytes=args.record_bytes, table_slots=args.table_slots)
 
     def barrier():
         if dist is not None:
