@@ -77,13 +77,13 @@ struct kc_ctx {
   unsigned long long *d_total_records = nullptr;
 
   // table
-  SlotA *d_A = nullptr;
-  uint64_t *d_B = nullptr;
+  Slot *d_A = nullptr;
+  uint4 *d_B = nullptr;      // N >= 3
+  uint32_t *d_C = nullptr;   // N >= 2
   uint64_t table_slots = 0, table_alloc_slots = 0;
   uint32_t *d_filter = nullptr;
   uint64_t filter_buckets = 0, filter_alloc_buckets = 0;
-  Overflow ovf{nullptr, nullptr, 0};
-  uint64_t ovf_alloc = 0;
+  Heavy heavy{nullptr, nullptr, nullptr, 0};
 
   DevCounters *d_ctr = nullptr;
   DevCounters h_ctr;
@@ -276,9 +276,11 @@ extern "C" void kc_destroy(kc_ctx *c) {
   dev_free(c->d_total_records);
   dev_free(c->d_A);
   dev_free(c->d_B);
+  dev_free(c->d_C);
   dev_free(c->d_filter);
-  dev_free(c->ovf.keys);
-  dev_free(c->ovf.ext);
+  dev_free(c->heavy.slots);
+  dev_free(c->heavy.side);
+  dev_free(c->heavy.n);
   dev_free(c->d_ctr);
   free_results(c->res_final);
   free_results(c->res_ext);
@@ -564,6 +566,8 @@ extern "C" int kc_exchange_recv_offsets(kc_ctx *c, uint64_t *offsets) {
 }
 
 // ------------------------------------------------------------------------------------------------ insert
+static uint64_t slot_bytes(int N) { return 32 + (N >= 2 ? 4 : 0) + (N >= 3 ? 16 : 0); }
+
 static uint64_t reference_table_slots(kc_ctx *c, uint64_t est_kmers) {
   // KmerDHT::KmerDHT + HashTableInserter::init: (kmers / depth + kmers * (1 - (1 - err)^k)) / 0.66
   // (src/kcount/kmer_dht.cpp:126-131, src/kcount/kcount_cpu.cpp:443-446); with the filter only the first term needs slots
@@ -589,9 +593,9 @@ static int ensure_table(kc_ctx *c) {
   // memory budget
   size_t free_b = 0, total_b = 0;
   CK(cudaMemGetInfo(&free_b, &total_b));
-  uint64_t have = (uint64_t)c->table_alloc_slots * (32 + 8 * (c->N - 1)) + c->filter_alloc_buckets * 32;
+  const uint64_t per_slot = slot_bytes(c->N);
+  uint64_t have = (uint64_t)c->table_alloc_slots * per_slot + c->filter_alloc_buckets * 32;
   uint64_t budget = c->cfg.mem_budget_bytes ? c->cfg.mem_budget_bytes : (uint64_t)((free_b + have) * 0.8);
-  uint64_t per_slot = 32 + 8 * (c->N - 1);
   if (buckets * 32 + slots * per_slot > budget) {
     if (c->cfg.table_slots) return fail(c, KC_ERR_NOMEM, "table of %llu slots does not fit the memory budget", (unsigned long long)slots);
     uint64_t fit = (budget - std::min(budget, buckets * 32)) / per_slot;
@@ -601,8 +605,10 @@ static int ensure_table(kc_ctx *c) {
   if (slots > c->table_alloc_slots) {
     dev_free(c->d_A);
     dev_free(c->d_B);
+    dev_free(c->d_C);
     CK(dev_alloc(&c->d_A, slots));
-    if (c->N > 1) CK(dev_alloc(&c->d_B, slots * (c->N - 1)));
+    if (c->N >= 2) CK(dev_alloc(&c->d_C, slots + 4));
+    if (c->N >= 3) CK(dev_alloc(&c->d_B, slots));
     c->table_alloc_slots = slots;
   }
   c->table_slots = slots;
@@ -612,19 +618,37 @@ static int ensure_table(kc_ctx *c) {
     c->filter_alloc_buckets = buckets;
   }
   c->filter_buckets = buckets;
-  // overflow side table: a key needs >= 65535 occurrences to get an entry
+  // heavy-key list: a key needs more than 65535 occurrences to get an entry
   uint64_t occ = std::max<uint64_t>(c->h_ctr.parse_counted * (uint64_t)c->G, 1);
-  uint64_t want = 1024;
-  while (want < 4 * (occ / 65535 + 1)) want *= 2;
-  if (want > c->ovf_alloc) {
-    dev_free(c->ovf.keys);
-    dev_free(c->ovf.ext);
-    CK(dev_alloc(&c->ovf.keys, want));
-    CK(dev_alloc(&c->ovf.ext, want * 8));
-    c->ovf_alloc = want;
+  uint64_t want = occ / 65536 + 64;
+  if (want > c->heavy.cap) {
+    dev_free(c->heavy.slots);
+    dev_free(c->heavy.side);
+    CK(dev_alloc(&c->heavy.slots, want));
+    CK(dev_alloc(&c->heavy.side, want * 8));
+    c->heavy.cap = want;
   }
-  c->ovf.mask = c->ovf_alloc - 1;
+  if (!c->heavy.n) CK(dev_alloc(&c->heavy.n, 1));
   return KC_OK;
+}
+
+static InsertParams insert_params(kc_ctx *c) {
+  InsertParams ip;
+  memset(&ip, 0, sizeof ip);
+  ip.k = c->k;
+  ip.rec_bytes = c->rec_bytes;
+  ip.n_segments = c->P * c->G;
+  ip.segments = c->d_segments;
+  ip.seg_tile_start = c->d_seg_tile_start;
+  ip.regions = c->d_regions;
+  ip.tile_records = insert_tile_records(c->rec_bytes);
+  ip.A = c->d_A;
+  ip.B = c->d_B;
+  ip.C = c->d_C;
+  ip.filter = c->d_filter;
+  ip.heavy = c->heavy;
+  ip.ctr = c->d_ctr;
+  return ip;
 }
 
 extern "C" int kc_insert(kc_ctx *c) {
@@ -656,18 +680,19 @@ extern "C" int kc_insert(kc_ctx *c) {
   CK(cudaStreamSynchronize(c->stream));
 
   CK(cudaEventRecord(c->ev0, c->stream));
-  // clear table, filter, overflow table and the insert-side counters
-  CK(cudaMemsetAsync(c->d_A, 0, c->table_slots * sizeof(SlotA), c->stream));
+  // clear table, filter and the insert-side counters
+  CK(cudaMemsetAsync(c->d_A, 0, c->table_slots * sizeof(Slot), c->stream));
+  if (c->N >= 2) CK(cudaMemsetAsync(c->d_C, 0, (c->table_slots + 4) * sizeof(uint32_t), c->stream));
+  if (c->N >= 3) CK(cudaMemsetAsync(c->d_B, 0, c->table_slots * sizeof(uint4), c->stream));
   if (c->filter_buckets) CK(cudaMemsetAsync(c->d_filter, 0, c->filter_buckets * 32, c->stream));
-  CK(cudaMemsetAsync(c->ovf.keys, 0, c->ovf_alloc * 8, c->stream));
-  CK(cudaMemsetAsync(c->ovf.ext, 0, c->ovf_alloc * 32, c->stream));
+  CK(cudaMemsetAsync(c->heavy.n, 0, sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(c->d_ctr, 0, offsetof(DevCounters, parse_counted), c->stream));
 
   PlanParams pp;
   pp.n_src = c->G;
   pp.local_bins = c->P;
   pp.rec_bytes = c->rec_bytes;
-  pp.tile_records = kTileRecords;
+  pp.tile_records = insert_tile_records(c->rec_bytes);
   pp.src_ptr = c->d_src_ptr;
   pp.segments = c->d_segments;
   pp.seg_tile_start = c->d_seg_tile_start;
@@ -678,47 +703,39 @@ extern "C" int kc_insert(kc_ctx *c) {
   CK(cudaEventRecord(c->ev_clr, c->stream));
   CK(launch_plan(pp, c->stream, &c->launches));
 
-  InsertParams ip;
-  memset(&ip, 0, sizeof ip);
-  ip.k = c->k;
-  ip.rec_bytes = c->rec_bytes;
-  ip.n_segments = n_seg;
-  ip.segments = c->d_segments;
-  ip.seg_tile_start = c->d_seg_tile_start;
-  ip.regions = c->d_regions;
-  ip.A = c->d_A;
-  ip.B = c->d_B;
-  ip.filter = c->d_filter;
-  ip.ovf = c->ovf;
-  ip.ctr = c->d_ctr;
-  const bool dedup = !(c->cfg.flags & KC_FLAG_NO_WARP_DEDUP);
+  InsertParams ip = insert_params(c);
+  const bool merge = !(c->cfg.flags & KC_FLAG_NO_WARP_DEDUP);
   CK(cudaEventRecord(c->ev_ik0, c->stream));
   c->stats.insert_kernel_launches = c->cfg.use_filter ? 2 : 1;
   if (!c->cfg.use_filter) {
-    CK(launch_insert(ip, c->N, MODE_INSERT, dedup, c->sm_count, c->stream, &c->launches));
+    CK(launch_insert(ip, c->N, MODE_INSERT, merge, c->sm_count, c->stream, &c->launches));
   } else {
     // exact singleton screen: pass A admits keys seen at least twice, pass B counts only admitted keys
-    CK(launch_insert(ip, c->N, MODE_ADMIT, dedup, c->sm_count, c->stream, &c->launches));
+    CK(launch_insert(ip, c->N, MODE_ADMIT, merge, c->sm_count, c->stream, &c->launches));
     CK(cudaMemsetAsync(&c->d_ctr->tile_cursor, 0, sizeof(unsigned long long), c->stream));
-    CK(launch_insert(ip, c->N, MODE_UPDATE, dedup, c->sm_count, c->stream, &c->launches));
+    CK(launch_insert(ip, c->N, MODE_UPDATE, merge, c->sm_count, c->stream, &c->launches));
   }
   CK(cudaEventRecord(c->ev_ik1, c->stream));
   CK(cudaEventRecord(c->ev1, c->stream));
   c->phase = PH_INSERTED;
-  free_results(c->res_final);
-  free_results(c->res_ext);
+  c->res_final.n = c->res_ext.n = 0;
+  c->res_final.sorted = c->res_ext.sorted = false;
   return KC_OK;
 }
 
 // ------------------------------------------------------------------------------------------------ finalize
+// result arrays are pooled: they only grow (the bench loop and iterative-k callers reuse them)
 static int alloc_results(kc_ctx *c, ResultSet &r, uint64_t cap, bool with_ext) {
+  r.n = 0;
+  r.sorted = false;
+  if (cap <= r.cap && r.keys && (!with_ext || r.ext8)) return KC_OK;
   free_results(r);
-  r.cap = cap;
-  CK(dev_alloc(&r.keys, cap * c->N));
-  CK(dev_alloc(&r.counts, cap));
-  CK(dev_alloc(&r.left, cap));
-  CK(dev_alloc(&r.right, cap));
-  if (with_ext) CK(dev_alloc(&r.ext8, cap * 8));
+  r.cap = cap + cap / 16 + 16;
+  CK(dev_alloc(&r.keys, r.cap * c->N));
+  CK(dev_alloc(&r.counts, r.cap));
+  CK(dev_alloc(&r.left, r.cap));
+  CK(dev_alloc(&r.right, r.cap));
+  if (with_ext) CK(dev_alloc(&r.ext8, r.cap * 8));
   return KC_OK;
 }
 
@@ -736,7 +753,7 @@ static void fill_stats(kc_ctx *c) {
   s.max_count = h.max_count;
   s.dropped = 0;
   s.table_slots = c->table_slots;
-  s.table_bytes = c->table_slots * (32 + 8 * (uint64_t)(c->N - 1));
+  s.table_bytes = c->table_slots * slot_bytes(c->N);
   s.filter_bytes = c->filter_buckets * 32;
   s.avg_kmer_count = h.n_final ? (double)h.sum_counts / (double)h.n_final : 0.0;
   s.kernel_launches = c->launches;
@@ -760,11 +777,11 @@ extern "C" int kc_finalize(kc_ctx *c, kc_stats *stats) {
     return fail(c, KC_ERR_TABLE_FULL, "k-mer table full (%llu slots, %llu keys placed): results undefined, enlarge table_slots",
                 (unsigned long long)c->table_slots, (unsigned long long)c->h_ctr.unique);
   }
-  if (c->h_ctr.err_ovf_full) return fail(c, KC_ERR_TABLE_FULL, "saturation side table full");
   const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
-  int rc = alloc_results(c, c->res_final, c->h_ctr.ge2, false);
+  // capacity: every key that owns a slot could survive (count >= 2 is only known after the pass)
+  int rc = alloc_results(c, c->res_final, c->h_ctr.unique, false);
   if (rc) return rc;
-  if (keep_ext && (rc = alloc_results(c, c->res_ext, c->h_ctr.ge2, true))) return rc;
+  if (keep_ext && (rc = alloc_results(c, c->res_ext, c->h_ctr.unique, true))) return rc;
 
   FinalizeParams fp;
   memset(&fp, 0, sizeof fp);
@@ -776,7 +793,8 @@ extern "C" int kc_finalize(kc_ctx *c, kc_stats *stats) {
   fp.n_slots = c->table_slots;
   fp.A = c->d_A;
   fp.B = c->d_B;
-  fp.ovf = c->ovf;
+  fp.C = c->d_C;
+  fp.heavy = c->heavy;
   fp.ctr = c->d_ctr;
   fp.out_keys = c->res_final.keys;
   fp.out_counts = c->res_final.counts;
@@ -791,6 +809,19 @@ extern "C" int kc_finalize(kc_ctx *c, kc_stats *stats) {
   fp.cap_ext = c->res_ext.cap;
   CK(cudaEventRecord(c->ev0, c->stream));
   CK(launch_finalize(fp, c->sm_count, c->stream, &c->launches));
+  unsigned long long n_heavy = 0;
+  CK(cudaMemcpyAsync(&n_heavy, c->heavy.n, sizeof n_heavy, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (n_heavy > c->heavy.cap) return fail(c, KC_ERR_STATE, "finalize: %llu keys with more than 65535 occurrences exceed the list of %llu",
+                                          n_heavy, (unsigned long long)c->heavy.cap);
+  if (n_heavy) {
+    // keys with more than 65535 occurrences: recount their extensions exactly from the resident supermers
+    CK(cudaMemsetAsync(c->heavy.side, 0, n_heavy * 8 * sizeof(uint32_t), c->stream));
+    CK(cudaMemsetAsync(&c->d_ctr->tile_cursor, 0, sizeof(unsigned long long), c->stream));
+    InsertParams ip = insert_params(c);
+    CK(launch_insert(ip, c->N, MODE_HEAVY, !(c->cfg.flags & KC_FLAG_NO_WARP_DEDUP), c->sm_count, c->stream, &c->launches));
+    CK(launch_finalize_heavy(fp, n_heavy, c->stream, &c->launches));
+  }
   CK(cudaEventRecord(c->ev1, c->stream));
   CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
@@ -833,8 +864,7 @@ extern "C" int kc_reset(kc_ctx *c) {
   if (!c) return KC_ERR_ARG;
   CK(cudaSetDevice(c->device));
   CK(cudaStreamSynchronize(c->stream));
-  free_results(c->res_final);
-  free_results(c->res_ext);
+  c->res_final.n = c->res_ext.n = 0;
   c->phase = PH_EMPTY;
   c->caps_valid = false;  // the next kc_parse samples the reads again, as a fresh stage would
   c->recv_off.clear();

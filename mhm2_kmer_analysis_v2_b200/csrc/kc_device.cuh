@@ -217,6 +217,28 @@ __device__ __forceinline__ void red_add32(void *p, uint32_t v) {
   asm volatile("red.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// 128-bit compare-and-swap (sm_90+): returns the previous value of the 16-byte aligned unit at p
+__device__ __forceinline__ ulonglong2 cas128(void *p, ulonglong2 cmp, ulonglong2 val) {
+  ulonglong2 old;
+  asm volatile(
+      "{\n\t.reg .b128 c, v, o;\n\t"
+      "mov.b128 c, {%2, %3};\n\t"
+      "mov.b128 v, {%4, %5};\n\t"
+      "atom.global.cas.b128 o, [%6], c, v;\n\t"
+      "mov.b128 {%0, %1}, o;\n\t}"
+      : "=l"(old.x), "=l"(old.y)
+      : "l"(cmp.x), "l"(cmp.y), "l"(val.x), "l"(val.y), "l"(p)
+      : "memory");
+  return old;
+}
+__device__ __forceinline__ ulonglong2 ld_cg128(const void *p) {
+  uint4 r = ld_cg16(p);
+  ulonglong2 v;
+  v.x = ((uint64_t)r.y << 32) | r.x;
+  v.y = ((uint64_t)r.w << 32) | r.z;
+  return v;
+}
+
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 
 }  // namespace kc

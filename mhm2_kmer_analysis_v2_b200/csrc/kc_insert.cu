@@ -5,20 +5,24 @@
 // (src/kcount/kcount_cpu.cpp:478-493, 339-355, 309-336, 232-271) and the reference's GPU kernel gpu_insert_supermer_block
 // with its TCF calls (src/kcount/kcount-gpu/gpu_hash_table.cpp:310-475, tcf_wrapper.hpp:96-178).
 //
-// A CTA pulls tiles of 256 supermer records (bin-major order, so the table region being hit stays L2 resident), stages
-// them in shared memory with 128-bit streaming loads, prefix-sums the k-mer counts and then works on a dense list of
-// k-mer occurrences: thread -> (record, k-mer) by binary search in shared memory. Per occurrence: extract the N key
-// words with funnel shifts, reverse-complement arithmetically, canonicalise and swap/complement the two extension bases
-// (kcount_cpu.cpp:326-333), merge equal (k-mer, extensions) inside the warp with __match_any_sync, probe the region
-// (linear probing, one 16-byte load per probe), claim with a single CAS (64-bit key for N == 1, 32-bit tag otherwise),
-// and add: one returning atomicAdd on the count, one 64-bit RED per extension word.
+// Every warp works on its own: it pulls a tile of supermer records (bin-major order, so the table region being hit stays
+// in L2), stages it in its slice of shared memory with 128-bit streaming loads, prefix-sums the k-mer counts with
+// shuffles and gives every lane an equal, CONTIGUOUS run of k-mer occurrences. A lane walks its run with a rolling
+// k-mer and a rolling reverse complement (one base in, one base out per step), canonicalises, swaps/complements the two
+// extension bases (kcount_cpu.cpp:326-333), merges equal consecutive occurrences (homopolymers) and then touches the
+// table: linear probing with one 16-byte load per probe, claim with a single CAS (64-bit for N == 1, 128-bit otherwise),
+// three fire-and-forget REDs (count, left word, right word). No block barrier, no fence, no returning atomic.
 #include "kc_internal.h"
 
 namespace kc {
 
 static const int THREADS = 256;
+static const int WARPS_PER_CTA = THREADS / 32;
 static const uint32_t MAX_PROBES = 1u << 16;
 static const uint64_t NOT_FOUND = ~0ULL;
+static const uint64_t NOT_READY = ~0ULL - 1;  // N >= 3: the slot's owner has not completed the key yet -- retry later
+
+int insert_tile_records(int rec_bytes) { return 2048 / rec_bytes; }  // 2 KB of records per warp tile: 128 / 64 / 32
 
 // ------------------------------------------------------------------------------------------------ planning
 __global__ void plan_kernel(PlanParams p) {
@@ -116,61 +120,56 @@ __device__ __forceinline__ bool filter_test_and_set(uint32_t *filter, const Regi
 }
 
 // ------------------------------------------------------------------------------------------------ table
+// Finds the slot of `key` inside the bin's region, claiming an empty one when CLAIM. Keys are stored complemented so
+// that an all-zero unit means "empty". N >= 3: the 16-byte unit B[slot] completes the key; it is written right after
+// the claim; a reader that matched the first two words and finds it still zero gets NOT_READY and retries the whole
+// occurrence on its next loop iteration (no spinning inside a warp: owner and reader may be lanes of the same warp).
 template <int N, bool CLAIM>
-__device__ __forceinline__ uint64_t find_or_claim(SlotA *A, uint64_t *B, const Region &rg, const uint64_t (&key)[N], uint64_t h,
+__device__ __forceinline__ uint64_t find_or_claim(Slot *A, uint4 *B, const Region &rg, const uint64_t (&key)[N], uint64_t h,
                                                   bool &is_new, DevCounters *ctr) {
   uint64_t idx = __umul64hi(h, rg.n_slots);
-  const uint32_t tag = (uint32_t)h | 2u;
   is_new = false;
+  ulonglong2 mine;
+  mine.x = ~key[0];
+  mine.y = N >= 2 ? ~key[1] : 0ULL;
+  ulonglong2 mineB;
+  mineB.x = N >= 3 ? ~key[N >= 3 ? 2 : 0] : 0ULL;
+  mineB.y = N >= 4 ? ~key[N >= 4 ? 3 : 0] : 0ULL;
 #pragma unroll 1
   for (uint32_t probe = 0; probe < MAX_PROBES && probe < rg.n_slots; probe++) {
-    SlotA *s = A + rg.slot_base + idx;
-    uint4 a = ld_cg16(s);
-    uint64_t k0 = ((uint64_t)a.y << 32) | a.x;
+    Slot *s = A + rg.slot_base + idx;
+    ulonglong2 a = ld_cg128(s);
+    bool match = false;
     if (N == 1) {
-      const uint64_t mine = ~key[0];
-      if (k0 == mine) return rg.slot_base + idx;
-      if (k0 == 0) {
+      if (a.x == mine.x) return rg.slot_base + idx;
+      if (a.x == 0) {
         if (!CLAIM) return NOT_FOUND;
-        unsigned long long old = atomicCAS(reinterpret_cast<unsigned long long *>(&s->key0x), 0ULL, (unsigned long long)mine);
+        unsigned long long old = atomicCAS(reinterpret_cast<unsigned long long *>(&s->k0x), 0ULL, (unsigned long long)mine.x);
         if (old == 0ULL) {
           is_new = true;
           return rg.slot_base + idx;
         }
-        if (old == mine) return rg.slot_base + idx;
+        if (old == mine.x) return rg.slot_base + idx;
       }
     } else {
-      uint32_t t = a.w;
-      uint64_t *kb = B + (rg.slot_base + idx) * (N - 1);
-      if (t == 0) {
+      if (a.x == 0 && a.y == 0) {
         if (!CLAIM) return NOT_FOUND;
-        uint32_t old = atomicCAS(&s->tag, 0u, 1u);
-        if (old == 0u) {
-          // slot is ours: write the key, then publish the tag (release orders the key stores before it)
-          *reinterpret_cast<volatile uint64_t *>(&s->key0x) = key[0];
-#pragma unroll
-          for (int j = 1; j < N; j++) *reinterpret_cast<volatile uint64_t *>(&kb[j - 1]) = key[j];
-          __threadfence();
-          st_release32(&s->tag, tag);
+        ulonglong2 zero;
+        zero.x = zero.y = 0;
+        ulonglong2 old = cas128(s, zero, mine);
+        if (old.x == 0 && old.y == 0) {
+          if (N >= 3) (void)cas128(B + rg.slot_base + idx, zero, mineB);  // completes the key; only the claimant writes it
           is_new = true;
           return rg.slot_base + idx;
         }
-        t = old;
-        k0 = ~key[0];  // force a re-read below
+        a = old;
       }
-      bool waited = false;
-      while (t == 1u) {  // another thread is writing this slot's key
-        t = ld_acquire32(&s->tag);
-        waited = true;
-      }
-      if (t == tag) {
-        if (waited || k0 != key[0]) k0 = ld_cg64(&s->key0x);
-        if (k0 == key[0]) {
-          bool same = true;
-#pragma unroll
-          for (int j = 1; j < N; j++) same = same && (ld_cg64(&kb[j - 1]) == key[j]);
-          if (same) return rg.slot_base + idx;
-        }
+      match = (a.x == mine.x && a.y == mine.y);
+      if (match) {
+        if (N == 2) return rg.slot_base + idx;
+        ulonglong2 b = ld_cg128(B + rg.slot_base + idx);
+        if (b.x == 0 && b.y == 0) return NOT_READY;  // claimant is about to write it
+        if (b.x == mineB.x && b.y == mineB.y) return rg.slot_base + idx;
       }
     }
     idx++;
@@ -180,209 +179,244 @@ __device__ __forceinline__ uint64_t find_or_claim(SlotA *A, uint64_t *B, const R
   return NOT_FOUND;
 }
 
-__device__ __forceinline__ void overflow_add(const Overflow &ovf, uint64_t slot, int l, int r, uint32_t v, DevCounters *ctr) {
-  uint64_t idx = (slot * 0x9e3779b97f4a7c15ULL >> 20) & ovf.mask;
-  for (uint64_t probe = 0; probe <= ovf.mask; probe++) {
-    unsigned long long cur = atomicCAS(reinterpret_cast<unsigned long long *>(&ovf.keys[idx]), 0ULL, (unsigned long long)(slot + 1));
-    if (cur == 0ULL || cur == slot + 1) {
-      uint32_t *e = ovf.ext + idx * 8;
-      if (l >= 0) {
-        uint32_t o = atomicAdd(&e[l], v);
-        if (o >= 0x80000000u) atomicSub(&e[l], v);
-      }
-      if (r >= 0) {
-        uint32_t o = atomicAdd(&e[4 + r], v);
-        if (o >= 0x80000000u) atomicSub(&e[4 + r], v);
-      }
-      return;
-    }
-    idx = (idx + 1) & ovf.mask;
-  }
-  ctr->err_ovf_full = 1u;
+template <int N>
+__device__ __forceinline__ uint32_t *count_ptr(Slot *A, uint32_t *C, uint64_t slot) {
+  return N == 1 ? reinterpret_cast<uint32_t *>(&A[slot].w1) : C + slot;
 }
 
-// count += cnt (u16 saturating), left[l] += cnt, right[r] += cnt with exact per-field saturation at 65535
-// (kcount_cpu.cpp:147-164, 349-353). Only the first 65535 occurrences of a key (in atomic order) touch the packed
-// 16-bit fields, so a field never carries into its neighbour; later ones go to the overflow table.
-__device__ __forceinline__ void add_counts(SlotA *s, uint64_t slot, uint32_t cnt, int l, int r, const Overflow &ovf,
-                                           DevCounters *ctr, uint32_t &ge2) {
-  uint32_t old = atomicAdd(&s->count, cnt);
-  if (old < 2u && old + cnt >= 2u) ge2++;
-  uint32_t fast = old >= 65535u ? 0u : min(cnt, 65535u - old);
-  uint32_t slow = cnt - fast;
-  if (fast) {
-    if (l >= 0) red_add64(&s->left, (uint64_t)fast << (16 * l));
-    if (r >= 0) red_add64(&s->right, (uint64_t)fast << (16 * r));
-  }
-  if (slow) {
-    atomicSub(&s->count, slow);  // keeps count within [65535, 65535 + occurrences in flight]: no 32-bit wrap
-    if (l >= 0 || r >= 0) overflow_add(ovf, slot, l, r, slow, ctr);
-  }
+// count += cnt, left[l] += cnt, right[r] += cnt. The packed 16-bit fields are exact while the key has at most 65535
+// occurrences; beyond that finalize discards them and uses the recount (MODE_HEAVY) instead.
+template <int N>
+__device__ __forceinline__ void add_counts(Slot *A, uint32_t *C, uint64_t slot, uint32_t cnt, int l, int r) {
+  red_add32(count_ptr<N>(A, C, slot), cnt);
+  if (l >= 0) red_add64(&A[slot].left, (uint64_t)cnt << (16 * l));
+  if (r >= 0) red_add64(&A[slot].right, (uint64_t)cnt << (16 * r));
 }
 
 // ------------------------------------------------------------------------------------------------ insert kernel
-template <int N, int MODE, bool DEDUP>
+template <int N>
+struct Occurrence {
+  uint64_t key[N];
+  int l, r;  // extension base codes 0..3, -1 = not counted (low quality / N)
+};
+
+// returns false when the occurrence has to be retried (NOT_READY); nothing has been counted then
+template <int N, int MODE>
+__device__ __forceinline__ bool apply_occurrence(const InsertParams &p, const Region &rg, const Occurrence<N> &o, uint32_t cnt,
+                                                 uint32_t &n_unique, uint32_t &n_filter_new) {
+  const uint64_t h = key_hash<N>(o.key);
+  bool is_new = false;
+  if (MODE == MODE_INSERT) {
+    uint64_t slot = find_or_claim<N, true>(p.A, p.B, rg, o.key, h, is_new, p.ctr);
+    if (N >= 3 && slot == NOT_READY) return false;
+    if (slot != NOT_FOUND) add_counts<N>(p.A, p.C, slot, cnt, o.l, o.r);
+  } else if (MODE == MODE_ADMIT) {
+    // (a retried occurrence finds its own tag and is treated as seen: it only admits a key early, which is harmless)
+    bool seen = filter_test_and_set(p.filter, rg, h);
+    if (!seen) n_filter_new++;
+    if (seen || cnt >= 2u) {
+      uint64_t slot = find_or_claim<N, true>(p.A, p.B, rg, o.key, h, is_new, p.ctr);
+      if (N >= 3 && slot == NOT_READY) return false;
+    }
+  } else if (MODE == MODE_UPDATE) {
+    uint64_t slot = find_or_claim<N, false>(p.A, p.B, rg, o.key, h, is_new, p.ctr);
+    if (slot < NOT_READY) add_counts<N>(p.A, p.C, slot, cnt, o.l, o.r);
+  } else {  // MODE_HEAVY: exact 32-bit extension counters of the keys finalize marked as heavy
+    uint64_t slot = find_or_claim<N, false>(p.A, p.B, rg, o.key, h, is_new, p.ctr);
+    if (slot < NOT_READY) {
+      uint32_t c = *count_ptr<N>(p.A, p.C, slot);
+      if (c & kHeavyMark) {
+        uint32_t *e = p.heavy.side + (uint64_t)(c & ~kHeavyMark) * 8;
+        if (o.l >= 0) atomicAdd(e + o.l, cnt);
+        if (o.r >= 0) atomicAdd(e + 4 + o.r, cnt);
+      }
+    }
+  }
+  if (is_new) n_unique++;
+  return true;
+}
+
+template <int N, int MODE, bool MERGE>
 __global__ void __launch_bounds__(THREADS) insert_kernel(InsertParams p) {
-  extern __shared__ __align__(16) uint32_t s_rec[];   // kTileRecords * W words, then kTileRecords + 1 prefix
-  __shared__ uint32_t s_warp_tot[THREADS / 32];
-  __shared__ unsigned long long s_tile;
-  __shared__ int s_seg;
-  const int tid = threadIdx.x;
+  extern __shared__ __align__(16) uint32_t s_all[];
   const uint32_t lane = lane_id();
+  const int warp = threadIdx.x >> 5;
   const int k = p.k;
   const int W = p.rec_bytes / 4;
+  const int T = p.tile_records;
   const int nbw = record_geom(p.rec_bytes, k).nbw;
-  uint32_t *s_pre = s_rec + kTileRecords * W;
+  uint32_t *s_rec = s_all + warp * (T * W + T + 4);  // this warp's records, then T + 1 prefix sums
+  uint32_t *s_pre = s_rec + T * W;
   const uint32_t n_tiles = p.seg_tile_start[p.n_segments];
-  const uint64_t last_mask = ~0ULL << (2 * (32 * N - k));  // valid bits of the last key word
+  const int tail = 2 * (32 * N - k);                 // unused low bits of the last key word
+  const uint64_t last_mask = ~0ULL << tail;
+  const int rpl = T / 32;                            // records per lane in the prefix step
 
-  uint32_t n_unique = 0, n_ge2 = 0, n_filter_new = 0, n_records = 0;
+  uint32_t n_unique = 0, n_filter_new = 0, n_records = 0;
   unsigned long long n_occ = 0;
 
   while (true) {
-    if (tid == 0) {
-      unsigned long long t = atomicAdd(&p.ctr->tile_cursor, 1ULL);
-      s_tile = t;
-      if (t < n_tiles) {
-        // segment of this tile: last i with seg_tile_start[i] <= t
-        int lo = 0, hi = p.n_segments;
+    // ---- next tile of this warp
+    unsigned long long tile = 0;
+    int seg = 0;
+    if (lane == 0) {
+      tile = atomicAdd(&p.ctr->tile_cursor, 1ULL);
+      if (tile < n_tiles) {
+        int lo = 0, hi = p.n_segments;  // last segment with seg_tile_start <= tile
         while (hi - lo > 1) {
           int mid = (lo + hi) >> 1;
-          if (p.seg_tile_start[mid] <= (uint32_t)t) lo = mid; else hi = mid;
+          if (p.seg_tile_start[mid] <= (uint32_t)tile) lo = mid; else hi = mid;
         }
-        s_seg = lo;
+        seg = lo;
       }
     }
-    __syncthreads();
-    const unsigned long long tile = s_tile;
+    tile = __shfl_sync(0xffffffffu, tile, 0);
+    seg = __shfl_sync(0xffffffffu, seg, 0);
     if (tile >= n_tiles) break;
-    const Segment sg = p.segments[s_seg];
+    const Segment sg = p.segments[seg];
     const Region rg = p.regions[sg.bin];
-    const uint32_t first = ((uint32_t)tile - p.seg_tile_start[s_seg]) * kTileRecords;
-    const int nrec = min((uint32_t)kTileRecords, sg.n_records - first);
+    const uint32_t first = ((uint32_t)tile - p.seg_tile_start[seg]) * T;
+    const int nrec = min((uint32_t)T, sg.n_records - first);
     // ---- stage the records (coalesced 16-byte streaming loads)
     {
       const uint4 *src = reinterpret_cast<const uint4 *>(sg.ptr + (uint64_t)first * p.rec_bytes);
       uint4 *dst = reinterpret_cast<uint4 *>(s_rec);
       const int n16 = nrec * (p.rec_bytes / 16);
-      for (int i = tid; i < n16; i += THREADS) dst[i] = ld_stream16(src + i);
+      for (int i = lane; i < n16; i += 32) dst[i] = ld_stream16(src + i);
     }
-    __syncthreads();
-    // ---- exclusive prefix sum of k-mers per record
-    uint32_t n_mine = (tid < nrec) ? (s_rec[tid * W + W - 1] & 0xffffu) : 0u;
-    if (n_mine) n_records++;
-    uint32_t incl = n_mine;
+    __syncwarp();
+    // ---- exclusive prefix sum of k-mers per record: lane handles records [lane * rpl, lane * rpl + rpl)
+    uint32_t mine = 0;
+    for (int u = 0; u < rpl; u++) {
+      int rr = lane * rpl + u;
+      uint32_t n = rr < nrec ? (s_rec[rr * W + W - 1] & 0xffffu) : 0u;
+      if (n) n_records++;
+      mine += n;
+    }
+    uint32_t incl = mine;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
       if ((int)lane >= o) incl += v;
     }
-    if (lane == 31) s_warp_tot[tid >> 5] = incl;
-    __syncthreads();
-    uint32_t warp_off = 0, total = 0;
-#pragma unroll
-    for (int wv = 0; wv < THREADS / 32; wv++) {
-      uint32_t t = s_warp_tot[wv];
-      if (wv < (tid >> 5)) warp_off += t;
-      total += t;
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    {
+      uint32_t at = incl - mine;
+      for (int u = 0; u < rpl; u++) {
+        int rr = lane * rpl + u;
+        s_pre[rr] = at;
+        at += rr < nrec ? (s_rec[rr * W + W - 1] & 0xffffu) : 0u;
+      }
+      if (lane == 31) s_pre[T] = total;
     }
-    s_pre[tid] = warp_off + incl - n_mine;
-    if (tid == 0) s_pre[kTileRecords] = total;
-    __syncthreads();
-    n_occ += (tid == 0) ? total : 0;
+    __syncwarp();
+    if (lane == 0) n_occ += total;
 
-    // ---- one k-mer occurrence per thread and step
-    for (uint32_t q0 = 0; q0 < total; q0 += THREADS) {
-      const uint32_t q = q0 + tid;
-      const bool valid = q < total;
-      uint64_t key[N];
-      uint64_t h = 0;
-      int l = -1, r = -1;
-      if (valid) {
-        int lo = 0, hi = kTileRecords;  // last record with s_pre[rec] <= q
-        while (hi - lo > 1) {
-          int mid = (lo + hi) >> 1;
-          if (s_pre[mid] <= q) lo = mid; else hi = mid;
-        }
-        const uint32_t *rec = s_rec + lo * W;
-        const int j = q - s_pre[lo];  // k-mer j of the record: bases [j+1, j+k], extensions at j and j+k+1
-        uint64_t fw[N], rc[N];
+    // ---- this lane's contiguous run of occurrences [q, qend)
+    const uint32_t per = (total + 31u) >> 5;
+    uint32_t q = min(total, lane * per);
+    const uint32_t qend = min(total, q + per);
+    int rec_i = 0, j = 0, n = 0;
+    const uint32_t *rec = s_rec;
+    uint64_t fw[N], rc[N];
+    bool fresh = true;
+    if (q < qend) {
+      int lo = 0, hi = T;  // last record with s_pre[rec] <= q (skips empty records)
+      while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (s_pre[mid] <= q) lo = mid; else hi = mid;
+      }
+      rec_i = lo;
+      j = q - s_pre[lo];
+      rec = s_rec + rec_i * W;
+      n = rec[W - 1] & 0xffffu;
+    }
+    Occurrence<N> pend;
+    uint32_t pend_cnt = 0;
+    while (true) {
+      const bool have = q < qend;
+      Occurrence<N> cur;
+      if (have) {
+        if (fresh) {  // k-mer j of the record: bases [j+1, j+k], extensions at j and j+k+1
 #pragma unroll
-        for (int i = 0; i < N; i++) fw[i] = rec_window64(rec, j + 1 + 32 * i);
-        fw[N - 1] &= last_mask;
-        revcomp_key<N>(fw, k, rc);
-        uint32_t lb = rec_base(rec, j), lq = rec_hq(rec, nbw, j);
-        uint32_t rb = rec_base(rec, j + k + 1), rq = rec_hq(rec, nbw, j + k + 1);
+          for (int i = 0; i < N; i++) fw[i] = rec_window64(rec, j + 1 + 32 * i);
+          fw[N - 1] &= last_mask;
+          revcomp_key<N>(fw, k, rc);
+          fresh = false;
+        }
+        const uint32_t lb = rec_base(rec, j), lq = rec_hq(rec, nbw, j);
+        const uint32_t rb = rec_base(rec, j + k + 1), rq = rec_hq(rec, nbw, j + k + 1);
         if (key_less<N>(rc, fw)) {  // kcount_cpu.cpp:328-333: swap and complement the extensions
 #pragma unroll
-          for (int i = 0; i < N; i++) key[i] = rc[i];
-          l = rq ? (int)(3u - rb) : -1;
-          r = lq ? (int)(3u - lb) : -1;
+          for (int i = 0; i < N; i++) cur.key[i] = rc[i];
+          cur.l = rq ? (int)(3u - rb) : -1;
+          cur.r = lq ? (int)(3u - lb) : -1;
         } else {
 #pragma unroll
-          for (int i = 0; i < N; i++) key[i] = fw[i];
-          l = lq ? (int)lb : -1;
-          r = rq ? (int)rb : -1;
+          for (int i = 0; i < N; i++) cur.key[i] = fw[i];
+          cur.l = lq ? (int)lb : -1;
+          cur.r = rq ? (int)rb : -1;
         }
-        h = key_hash<N>(key);
       }
-      uint32_t cnt = valid ? 1u : 0u;
-      if (DEDUP) {
-        // merge identical (k-mer, extensions) inside the warp: the first lane of each group works for all
-        const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
-        if (valid) {
-          const uint64_t ident = h ^ ((uint64_t)(l + 1) * 0x9e3779b97f4a7c15ULL) ^ ((uint64_t)(r + 1) * 0xc2b2ae3d27d4eb4fULL);
-          const uint32_t peers = __match_any_sync(vmask, ident);
-          const int leader = __ffs(peers) - 1;
-          bool same = true;  // a 64-bit match is only a hint: compare the real key with the leader's
+      bool same = false;
+      if (MERGE && have && pend_cnt) {
+        same = cur.l == pend.l && cur.r == pend.r;
 #pragma unroll
-          for (int i = 0; i < N; i++) same = same && (__shfl_sync(peers, key[i], leader) == key[i]);
-          same = same && (__shfl_sync(peers, l * 8 + r, leader) == l * 8 + r);
-          const uint32_t diff = __ballot_sync(peers, !same);
-          if (diff == 0u)
-            cnt = ((int)lane == leader) ? __popc(peers) : 0u;
-          // else: hash collision inside the group -- every lane inserts its own occurrence
-        }
+        for (int i = 0; i < N; i++) same = same && cur.key[i] == pend.key[i];
       }
-      if (cnt) {
-        bool is_new = false;
-        uint64_t slot = NOT_FOUND;
-        if (MODE == MODE_INSERT) {
-          slot = find_or_claim<N, true>(p.A, p.B, rg, key, h, is_new, p.ctr);
-        } else if (MODE == MODE_ADMIT) {
-          bool seen = filter_test_and_set(p.filter, rg, h);
-          if (!seen) n_filter_new++;
-          if (seen || cnt >= 2u) (void)find_or_claim<N, true>(p.A, p.B, rg, key, h, is_new, p.ctr);
-        } else {
-          slot = find_or_claim<N, false>(p.A, p.B, rg, key, h, is_new, p.ctr);
+      if (same) {
+        pend_cnt++;
+      } else {
+        if (pend_cnt && !apply_occurrence<N, MODE>(p, rg, pend, pend_cnt, n_unique, n_filter_new)) continue;  // retry
+        if (!have) break;
+        pend = cur;
+        pend_cnt = 1;
+      }
+      // ---- advance to the next occurrence of the run
+      q++;
+      j++;
+      if (q < qend) {
+        if (j == n) {  // next non-empty record
+          do {
+            rec_i++;
+            rec += W;
+            n = rec[W - 1] & 0xffffu;
+          } while (n == 0);
+          j = 0;
+          fresh = true;
+        } else {  // roll: base j+k enters, base j leaves
+          const uint64_t b = rec_base(rec, j + k);
+#pragma unroll
+          for (int i = 0; i < N - 1; i++) fw[i] = (fw[i] << 2) | (fw[i + 1] >> 62);
+          fw[N - 1] = (fw[N - 1] << 2) | (b << tail);
+#pragma unroll
+          for (int i = N - 1; i > 0; i--) rc[i] = (rc[i] >> 2) | (rc[i - 1] << 62);
+          rc[0] = (rc[0] >> 2) | ((3ULL - b) << 62);
+          rc[N - 1] &= last_mask;
         }
-        if (is_new) n_unique++;
-        if (MODE != MODE_ADMIT && slot != NOT_FOUND) add_counts(p.A + slot, slot, cnt, l, r, p.ovf, p.ctr, n_ge2);
       }
     }
-    __syncthreads();  // tile buffer is reused
+    __syncwarp();  // the tile buffer is reused
   }
 
   // ---- statistics: warp reduce, one atomic per warp and counter
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     n_unique += __shfl_down_sync(0xffffffffu, n_unique, o);
-    n_ge2 += __shfl_down_sync(0xffffffffu, n_ge2, o);
     n_filter_new += __shfl_down_sync(0xffffffffu, n_filter_new, o);
     n_records += __shfl_down_sync(0xffffffffu, n_records, o);
   }
   if (lane == 0) {
     if (n_unique) atomicAdd(&p.ctr->unique, (unsigned long long)n_unique);
-    if (n_ge2) atomicAdd(&p.ctr->ge2, (unsigned long long)n_ge2);
     if (n_filter_new) atomicAdd(&p.ctr->filter_new, (unsigned long long)n_filter_new);
-    if (n_records && MODE != MODE_UPDATE) atomicAdd(&p.ctr->records_in, (unsigned long long)n_records);
+    if (n_records && (MODE == MODE_INSERT || MODE == MODE_ADMIT)) atomicAdd(&p.ctr->records_in, (unsigned long long)n_records);
+    if (n_occ && (MODE == MODE_INSERT || MODE == MODE_ADMIT)) atomicAdd(&p.ctr->occurrences, n_occ);
   }
-  if (tid == 0 && n_occ && MODE != MODE_UPDATE) atomicAdd(&p.ctr->occurrences, n_occ);
 }
 
 template <int N, int MODE>
-static cudaError_t launch_insert_nm(const InsertParams &p, bool dedup, int grid, size_t smem, cudaStream_t s) {
-  if (dedup) {
+static cudaError_t launch_insert_nm(const InsertParams &p, bool merge, int grid, size_t smem, cudaStream_t s) {
+  if (merge) {
     cudaFuncSetAttribute(insert_kernel<N, MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     insert_kernel<N, MODE, true><<<grid, THREADS, smem, s>>>(p);
   } else {
@@ -393,28 +427,27 @@ static cudaError_t launch_insert_nm(const InsertParams &p, bool dedup, int grid,
 }
 
 template <int N>
-static cudaError_t launch_insert_n(const InsertParams &p, int mode, bool dedup, int grid, size_t smem, cudaStream_t s) {
+static cudaError_t launch_insert_n(const InsertParams &p, int mode, bool merge, int grid, size_t smem, cudaStream_t s) {
   switch (mode) {
-    case MODE_INSERT: return launch_insert_nm<N, MODE_INSERT>(p, dedup, grid, smem, s);
-    case MODE_ADMIT: return launch_insert_nm<N, MODE_ADMIT>(p, dedup, grid, smem, s);
-    case MODE_UPDATE: return launch_insert_nm<N, MODE_UPDATE>(p, dedup, grid, smem, s);
+    case MODE_INSERT: return launch_insert_nm<N, MODE_INSERT>(p, merge, grid, smem, s);
+    case MODE_ADMIT: return launch_insert_nm<N, MODE_ADMIT>(p, merge, grid, smem, s);
+    case MODE_UPDATE: return launch_insert_nm<N, MODE_UPDATE>(p, merge, grid, smem, s);
+    case MODE_HEAVY: return launch_insert_nm<N, MODE_HEAVY>(p, merge, grid, smem, s);
   }
   return cudaErrorInvalidValue;
 }
 
-cudaError_t launch_insert(const InsertParams &p, int n_words, int mode, bool dedup, int sm_count, cudaStream_t s, uint64_t *launches) {
-  const size_t smem = (size_t)kTileRecords * p.rec_bytes + (kTileRecords + 1) * sizeof(uint32_t);
-  // persistent CTAs: as many as stay resident (shared memory bound for 64-byte records), tiles are pulled dynamically
-  int per_sm = (int)((200 * 1024) / (smem + 1024));
-  if (per_sm > 8) per_sm = 8;
-  if (per_sm < 1) per_sm = 1;
-  const int grid = sm_count * per_sm;
+cudaError_t launch_insert(const InsertParams &p, int n_words, int mode, bool merge, int sm_count, cudaStream_t s, uint64_t *launches) {
+  const size_t per_warp = ((size_t)p.tile_records * p.rec_bytes / 4 + p.tile_records + 4) * sizeof(uint32_t);
+  const size_t smem = per_warp * WARPS_PER_CTA;
+  // persistent warps: as many CTAs as stay resident (register bound), tiles are pulled dynamically
+  const int grid = sm_count * 4;
   (*launches)++;
   switch (n_words) {
-    case 1: return launch_insert_n<1>(p, mode, dedup, grid, smem, s);
-    case 2: return launch_insert_n<2>(p, mode, dedup, grid, smem, s);
-    case 3: return launch_insert_n<3>(p, mode, dedup, grid, smem, s);
-    case 4: return launch_insert_n<4>(p, mode, dedup, grid, smem, s);
+    case 1: return launch_insert_n<1>(p, mode, merge, grid, smem, s);
+    case 2: return launch_insert_n<2>(p, mode, merge, grid, smem, s);
+    case 3: return launch_insert_n<3>(p, mode, merge, grid, smem, s);
+    case 4: return launch_insert_n<4>(p, mode, merge, grid, smem, s);
   }
   return cudaErrorInvalidValue;
 }

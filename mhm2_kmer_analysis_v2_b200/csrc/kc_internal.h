@@ -9,27 +9,30 @@
 namespace kc {
 
 // ---- hash table ---------------------------------------------------------------
-// One 32-byte, sector-aligned block per slot holds everything an insert touches after the key compare:
-//   N == 1 : key0x = ~key (0 = empty), claimed with one 64-bit CAS; tag unused
-//   N >= 2 : key0x = key word 0; tag = 0 empty / 1 being written / (hash fingerprint | 2) published;
-//            key words 1..N-1 live in the side array keyB[(N-1) * slot]
-// left/right pack four saturating 16-bit counters (A,C,G,T at bits 0,16,32,48); count is 32-bit and is
-// kept from running past 65535 + (occurrences in flight) -- see add_counts() in kc_insert.cu.
-struct alignas(32) SlotA {
-  uint64_t key0x;
-  uint32_t count;
-  uint32_t tag;
+// One 32-byte, sector-aligned block per slot holds what an insert touches:
+//   N == 1 : k0x = ~key word 0 (0 = empty), w1 = 32-bit occurrence count (low half)
+//   N >= 2 : k0x = ~key word 0, w1 = ~key word 1 (both 0 = empty; a canonical key never complements to 0 because the
+//            unused trailing bits of its last word are 0), claimed with ONE 128-bit CAS; the 32-bit occurrence count
+//            lives in the dense side array C[slot]; key words 2..3 live in B[slot] (16 bytes, complemented, 0 = not yet
+//            written -- readers that matched k0x/w1 wait for it)
+// left/right pack four 16-bit counters (A,C,G,T at bits 0,16,32,48). Every update is a fire-and-forget RED: no
+// returning atomic, no fence. A key with more than 65535 occurrences ("heavy", e.g. a homopolymer) may carry between
+// its packed fields; finalize detects it from the 32-bit count and recounts its extensions exactly (Heavy below).
+struct alignas(32) Slot {
+  uint64_t k0x;
+  uint64_t w1;
   uint64_t left;
   uint64_t right;
 };
-static_assert(sizeof(SlotA) == 32, "slot block must be one 32-byte sector");
+static_assert(sizeof(Slot) == 32, "slot block must be one 32-byte sector");
 
-// extension increments that arrive after a k-mer's count reached 65535 go to this small side table so
-// that the packed 16-bit fields can never carry into each other (exact u16 saturation, kcount_cpu.cpp:147-164)
-struct Overflow {
-  uint64_t *keys;  // slot index + 1, 0 = empty
-  uint32_t *ext;   // 8 counters per entry
-  uint64_t mask;   // capacity - 1
+static const uint32_t kHeavyMark = 0x80000000u;  // count field of a heavy slot after detection: kHeavyMark | heavy index
+
+struct Heavy {
+  uint64_t *slots;            // [cap] slot index of each heavy key
+  uint32_t *side;             // [cap * 8] exact extension counters lA lC lG lT rA rC rG rT, filled by the recount pass
+  unsigned long long *n;      // number of heavy keys found by finalize (may exceed cap: then it is an error)
+  uint64_t cap;
 };
 
 struct Region {  // table / filter range owned by one local bin
@@ -43,19 +46,19 @@ struct Segment {  // run of supermer records of one (source rank, local bin)
   uint32_t bin;
 };
 
-enum InsertMode { MODE_INSERT = 0, MODE_ADMIT = 1, MODE_UPDATE = 2 };
+enum InsertMode { MODE_INSERT = 0, MODE_ADMIT = 1, MODE_UPDATE = 2, MODE_HEAVY = 3 };
 
 struct DevCounters {  // device-resident, zeroed by kc_reset
   unsigned long long tile_cursor;
   unsigned long long unique;        // keys that claimed a table slot
-  unsigned long long ge2;           // keys whose count reached 2
+  unsigned long long ge2;           // keys with count >= 2 (counted by finalize)
   unsigned long long occurrences;   // k-mer occurrences inserted
   unsigned long long records_in;    // non-empty supermer records consumed
   unsigned long long filter_new;    // first sightings registered by the filter
   unsigned long long n_final, n_ext;  // finalize output cursors
   unsigned long long sum_counts, max_count;
   unsigned long long purged;
-  unsigned int err_table_full, err_ovf_full;
+  unsigned int err_table_full, err_heavy_full;
   unsigned long long parse_counted, parse_records, parse_raw;
   unsigned int err_bins_full;
 };
@@ -65,10 +68,12 @@ struct InsertParams {
   const Segment *segments;
   const uint32_t *seg_tile_start;  // [n_segments + 1] exclusive prefix of tiles
   const Region *regions;
-  SlotA *A;
-  uint64_t *B;
+  int tile_records;  // records per warp tile
+  Slot *A;
+  uint4 *B;          // N >= 3: key words 2..3 (complemented)
+  uint32_t *C;       // N >= 2: occurrence counts
   uint32_t *filter;  // 8 u32 words (16 tags) per bucket
-  Overflow ovf;
+  Heavy heavy;       // MODE_HEAVY only
   DevCounters *ctr;
 };
 
@@ -76,9 +81,10 @@ struct FinalizeParams {
   int k, n_words, dmin_thres, keep_ext;
   double dyn_min_depth;
   uint64_t n_slots;
-  const SlotA *A;
-  const uint64_t *B;
-  Overflow ovf;
+  Slot *A;
+  const uint4 *B;
+  uint32_t *C;
+  Heavy heavy;
   DevCounters *ctr;
   // survivors (D1)
   uint64_t *out_keys;
@@ -129,12 +135,14 @@ struct PlanParams {
 cudaError_t launch_plan(const PlanParams &p, cudaStream_t s, uint64_t *launches);
 cudaError_t launch_write_headers(uint8_t *const *dst_header, const uint64_t *bin_base, const unsigned long long *bin_cursor,
                                  const uint64_t *bin_cap, int n_ranks, int local_bins, cudaStream_t s, uint64_t *launches);
-cudaError_t launch_insert(const InsertParams &p, int n_words, int mode, bool dedup, int sm_count, cudaStream_t s, uint64_t *launches);
+cudaError_t launch_insert(const InsertParams &p, int n_words, int mode, bool merge_runs, int sm_count, cudaStream_t s, uint64_t *launches);
 cudaError_t launch_finalize(const FinalizeParams &p, int sm_count, cudaStream_t s, uint64_t *launches);
+// second finalize step for the heavy keys listed by launch_finalize, after the MODE_HEAVY recount
+cudaError_t launch_finalize_heavy(const FinalizeParams &p, uint64_t n_heavy, cudaStream_t s, uint64_t *launches);
+int insert_tile_records(int rec_bytes);
 cudaError_t launch_checksum(const uint64_t *keys, const uint16_t *counts, const char *left, const char *right, const uint16_t *ext8,
                             uint64_t n, int n_words, unsigned long long *out, cudaStream_t s, uint64_t *launches);
 
-static const int kTileRecords = 256;  // supermer records staged in shared memory per insert tile
 static const int kHeaderAlign = 64;
 
 }  // namespace kc
