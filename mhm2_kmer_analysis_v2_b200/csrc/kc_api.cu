@@ -13,12 +13,6 @@
 #include "kc_internal.h"
 #include "kcount_b200.h"
 
-namespace kc {
-int parse_grid_size(uint64_t n_reads, uint32_t read_stride, int sm_count);
-int parse_resv_records();
-int parse_warps_per_block();
-}  // namespace kc
-
 using namespace kc;
 
 static thread_local std::string g_create_error;
@@ -179,7 +173,7 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   if (cfg->n_ranks < 1 || cfg->rank < 0 || cfg->rank >= cfg->n_ranks) return fail(c, KC_ERR_ARG, "kc_create: bad rank %d/%d", cfg->rank, cfg->n_ranks);
   int m = cfg->m ? (int)cfg->m : reference_minimizer_len(cfg->k);
   if (m > (int)cfg->k) m = cfg->k;
-  if (m < 1 || m > 31) return fail(c, KC_ERR_ARG, "kc_create: minimizer length %d unsupported (1..31)", m);
+  if (m < 1 || m > 28) return fail(c, KC_ERR_ARG, "kc_create: minimizer length %d unsupported (1..28)", m);
   uint32_t P = cfg->local_bins ? cfg->local_bins : 1;
   if (P & (P - 1)) return fail(c, KC_ERR_ARG, "kc_create: local_bins must be a power of two");
   if ((uint64_t)P * cfg->n_ranks > 65536) return fail(c, KC_ERR_ARG, "kc_create: too many bins");
@@ -404,13 +398,7 @@ static int layout_bins(kc_ctx *c, const std::vector<uint64_t> &cap) {
   return KC_OK;
 }
 
-static uint64_t reservation_pad(kc_ctx *c) {
-  if (c->n_ids > 32) return 64;
-  uint64_t pad = parse_resv_records();
-  for (auto &ch : c->chunks)
-    pad += (uint64_t)parse_grid_size(ch.n_reads, 1, c->sm_count) * parse_warps_per_block() * parse_resv_records();
-  return pad;
-}
+static uint64_t reservation_pad(kc_ctx *) { return 64; }
 
 // capacity estimate from a strided sample of the reads (count-only run of the parse kernel)
 static int estimate_caps(kc_ctx *c) {
@@ -435,7 +423,6 @@ static int estimate_caps(kc_ctx *c) {
     double cnt = (double)c->h_cursor[i];
     double est = cnt * stride;
     if (stride > 1) est += 6.0 * stride * std::sqrt(cnt + 1.0) + 0.02 * est;
-    if (c->n_ids <= 32) est *= 1.15;  // reservation tails (kc_parse.cu)
     cap[i] = (uint64_t)est + pad;
   }
   int rc = layout_bins(c, cap);
@@ -477,7 +464,7 @@ extern "C" int kc_parse(kc_ctx *c) {
     // the sample under-estimated a bin: the cursors now hold the exact demand, lay out again and redo
     std::vector<uint64_t> cap(c->n_ids);
     const uint64_t pad = reservation_pad(c);
-    for (uint32_t i = 0; i < c->n_ids; i++) cap[i] = (c->n_ids <= 32 ? 2 : 1) * c->h_cursor[i] + pad;
+    for (uint32_t i = 0; i < c->n_ids; i++) cap[i] = c->h_cursor[i] + pad;
     rc = layout_bins(c, cap);
     if (rc) return rc;
     rc = run_parse(c);

@@ -4,66 +4,84 @@
 // SeqBlockInserter::process_seq (src/kcount/kcount_cpu.cpp:74-103) and the reference's GPU kernels parse_and_pack /
 // build_supermers / pack_seqs (src/kcount/kcount-gpu/parse_and_pack.cpp:127-237).
 //
-// One warp owns one read (in segments of <= 256 bases). The bytes (base | qual << 3, src/packed_reads.cpp:99-126)
-// are turned into bit planes with three ballots per 32 bases, interleaved into the 2-bit Kmer word layout and kept in
-// shared memory together with a "high quality" bit plane. N becomes (G, low quality): inside a k-mer the reference maps
-// N to G (src/kmer.cpp:173,191-192) and as an extension an N is never counted (kcount_cpu.cpp:157-164).
-// Canonical m-mers are taken per position with a funnel shift + bit-reversal, the reference's "greatest least-complement
-// m-mer" minimizer (src/kmer.cpp:345-398) is a sliding-window maximum computed by max-doubling, the owner is
-// quick_hash(minimizer) % n_ranks (src/kcount/kmer_dht.cpp:193-196) and the local bin (hash / n_ranks) & (bins-1).
-// Runs of equal (owner, bin) are found with ballots; each run (cut to the record capacity) becomes one fixed-size
-// supermer record written with 128-bit stores into the per-(owner, bin) area of the send buffer.
+// A warp takes 32 consecutive reads, one per lane.
+//   (1) pack: every lane reads its bytes (base | qual << 3, src/packed_reads.cpp:99-126) with aligned 128-bit loads and
+//       turns 16 bytes into one 32-bit word of 2-bit codes (Kmer word layout, src/kmer.cpp:303-325) plus 16 "high
+//       quality" bits, kept in shared memory. N becomes (G, low quality): inside a k-mer the reference maps N to G
+//       (src/kmer.cpp:173,191-192) and as an extension an N is never counted (kcount_cpu.cpp:157-164).
+//   (2) scan: the lane walks its read once with a rolling forward and reverse-complement m-mer; the reference's
+//       "greatest least-complement m-mer" minimizer (src/kmer.cpp:345-398) of every k-mer is a sliding-window maximum,
+//       computed with the block prefix/suffix-maximum scheme (all lanes stay in lock step, no data-dependent loops).
+//       A run of k-mers with the same minimizer (cut to the record capacity) is one supermer.
+//   (3) emit: finished runs go to a small per-warp queue; whenever 32 are queued every lane takes one: owner =
+//       quick_hash(minimizer) % n_ranks (src/kcount/kmer_dht.cpp:193-196), local bin = (hash / n_ranks) & (bins-1), one
+//       cursor update per distinct bin in the batch, and the fixed-size record is cut out of the owning lane's packed
+//       words with funnel shifts and written with 128-bit stores into the per-(owner, bin) area of the send buffer.
 #include "kc_internal.h"
 
 namespace kc {
 
-static const int SEG = 256;       // bases of a read handled per warp iteration
-static const int WARPS = 8;       // warps per CTA
-static const int RESV = 64;       // records reserved per (warp, bin) at a time on the few-bins path
+static const int SEG = 256;                            // bases of a read handled per lane and pass
+static const int NW = (SEG + 16 + 160) / 16 + 2;       // packed base words per lane (16 bases each) incl. lead + read-ahead
+static const int NQ = (SEG + 16 + 160) / 32 + 2;       // quality-bit words per lane
+static const int QCAP = 64;                            // queue entries per warp
 
-struct WarpSmem {
-  uint64_t W[SEG / 32 + 2];   // 2-bit packed bases of the segment (+ zero padding for window reads)
-  uint32_t Q[SEG / 32 + 2];   // high-quality bit plane, base j at bit 31 - j%32
-  uint64_t C[SEG];            // canonical m-mers, then running window maxima
-  uint32_t ID[SEG];           // (owner, bin) id per counted k-mer
-  unsigned long long resv_base[32];
-  uint32_t resv_used[32];
-};
-
-template <int R>
-__device__ __forceinline__ void write_empty(uint8_t *bins, uint64_t byte_base, uint64_t slot) {
-  *reinterpret_cast<uint32_t *>(bins + byte_base + slot * R + (R - 4)) = 0u;
+// 4 PackedRead bytes (first base in the lowest byte) -> 8 bits of 2-bit codes (first base highest) + 4 quality bits
+__device__ __forceinline__ void pack4(uint32_t x, uint32_t cut_add, uint32_t &codes8, uint32_t &hq4) {
+  const uint32_t is_n = (x >> 2) & 0x01010101u;          // base code 4 = N
+  const uint32_t lo2 = (x & 0x03030303u) | (is_n << 1);  // N -> G (2)
+  const uint32_t q = (x >> 3) & 0x1f1f1f1fu;
+  const uint32_t hq = ((q + cut_add) >> 5) & 0x01010101u & ~is_n;  // q >= cutoff, and never for N
+  codes8 = (lo2 * 0x40100401u) >> 24;
+  hq4 = ((hq * 0x08040201u) >> 24) & 0xfu;
 }
 
-// build one record for k-mers [start, start + n) of the segment (segment-relative k-mer index = index of the
-// record's first base) and store it
+struct WarpQueue {
+  uint64_t val[QCAP];   // minimizer (right aligned)
+  uint32_t meta[QCAP];  // owner lane | lead << 5 | first k-mer << 9 | k-mers << 17
+};
+
+// build the record for k-mers [start, start + n) of the segment held by lane `owner` and store it at dst
 template <int R>
-__device__ __forceinline__ void write_record(const WarpSmem &sm, uint8_t *dst, int start, int n, int k) {
+__device__ __forceinline__ void write_record(const uint32_t *s_w, const uint32_t *s_q, int owner, int lead, int start, int n, int k,
+                                             uint8_t *dst) {
   constexpr int W = R / 4;
   constexpr int NBW = (R == 16 ? 32 : (R == 32 ? 80 : 160)) / 16;
   constexpr int NQW = W - NBW - (R == 32 ? 0 : 1);  // R=32: third quality word shares the header word
   const int nbases = n + k + 1;
+  const int p0 = lead + start;  // position of the record's first base in the lane's packed stream
   uint32_t w[W];
+  {
+    const int q = p0 >> 4, sh = (p0 & 15) * 2;
+    uint32_t prev = s_w[q * 32 + owner];
 #pragma unroll
-  for (int u = 0; u < NBW; u++) {
-    int valid = nbases - 16 * u;
-    uint32_t x = 0;
-    if (valid > 0) {
-      x = (uint32_t)(window64(sm.W, start + 16 * u) >> 32);
-      if (valid < 16) x &= ~(0xffffffffu >> (2 * valid));
+    for (int u = 0; u < NBW; u++) {
+      const int valid = nbases - 16 * u;
+      uint32_t x = 0;
+      if (valid > 0) {
+        const uint32_t next = s_w[(q + u + 1) * 32 + owner];
+        x = __funnelshift_l(next, prev, sh);
+        prev = next;
+        if (valid < 16) x &= ~(0xffffffffu >> (2 * valid));
+      }
+      w[u] = x;
     }
-    w[u] = x;
   }
+  {
+    const int q = p0 >> 5, sh = p0 & 31;
+    uint32_t prev = s_q[q * 32 + owner];
 #pragma unroll
-  for (int v = 0; v < NQW; v++) {
-    int valid = nbases - 32 * v;
-    uint32_t x = 0;
-    if (valid > 0) {
-      int pos = start + 32 * v, q = pos >> 5, s = pos & 31;
-      x = __funnelshift_l(sm.Q[q + 1], sm.Q[q], s);
-      if (valid < 32) x &= ~(0xffffffffu >> valid);
+    for (int v = 0; v < NQW; v++) {
+      const int valid = nbases - 32 * v;
+      uint32_t x = 0;
+      if (valid > 0) {
+        const uint32_t next = s_q[(q + v + 1) * 32 + owner];
+        x = __funnelshift_l(next, prev, sh);
+        prev = next;
+        if (valid < 32) x &= ~(0xffffffffu >> valid);
+      }
+      w[NBW + v] = x;
     }
-    w[NBW + v] = x;
   }
   if (R == 32)
     w[W - 1] = (w[W - 1] & 0xffff0000u) | (uint32_t)n;
@@ -73,191 +91,231 @@ __device__ __forceinline__ void write_record(const WarpSmem &sm, uint8_t *dst, i
   for (int i = 0; i < W / 4; i++) st_stream16(dst + 16 * i, make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]));
 }
 
-template <int R, bool FEWBINS>
-__global__ void __launch_bounds__(WARPS * 32) parse_kernel(ParseParams p) {
-  __shared__ WarpSmem smem[WARPS];
-  const int warp = threadIdx.x >> 5;
+// every lane < nd takes one queued run: bin id, slot in the bin, record
+template <int R>
+__device__ __forceinline__ void drain(const ParseParams &p, const uint32_t *s_w, const uint32_t *s_q, WarpQueue &Q, uint32_t &q_head,
+                                      uint32_t &q_count, unsigned long long &n_records) {
   const uint32_t lane = lane_id();
-  WarpSmem &sm = smem[warp];
+  const uint32_t nd = min(32u, q_count);
+  __syncwarp();
+  const bool mine = lane < nd;
+  uint32_t id = 0, meta = 0;
+  if (mine) {
+    const uint32_t e = (q_head + lane) & (QCAP - 1);
+    meta = Q.meta[e];
+    if (p.n_ids > 1) {
+      const uint64_t mz = Q.val[e] << (64 - 2 * p.m);  // left aligned as Kmer::get_minimizer_fast returns it
+      uint64_t h = quick_hash(mz), q;
+      uint32_t owner;
+      fast_divmod(h, p.div_ranks, q, owner);
+      id = owner * (p.bins_mask + 1u) + ((uint32_t)q & p.bins_mask);
+    }
+  }
+  // one cursor update per distinct bin of the batch (full-mask collectives: all lanes take part, idle ones stand alone)
+  const uint32_t peers = p.n_ids > 1 ? __match_any_sync(0xffffffffu, mine ? id : (0x80000000u | lane)) : __ballot_sync(0xffffffffu, mine);
+  const int leader = mine ? __ffs(peers) - 1 : (int)lane;
+  unsigned long long slot0 = 0;
+  if (mine && (int)lane == leader) slot0 = atomicAdd(&p.bin_cursor[id], (unsigned long long)__popc(peers));
+  slot0 = __shfl_sync(0xffffffffu, slot0, leader);
+  if (mine) {
+    if (!p.count_only) {
+      const unsigned long long slot = slot0 + __popc(peers & ((1u << lane) - 1u));
+      if (slot < p.bin_cap[id])
+        write_record<R>(s_w, s_q, meta & 31u, (meta >> 5) & 15u, (meta >> 9) & 255u, (meta >> 17) & 255u, p.k,
+                        p.bins + p.bin_base[id] + slot * R);
+      else
+        p.ctr->err_bins_full = 1u;
+    }
+    n_records++;
+  }
+  q_head = (q_head + nd) & (QCAP - 1);
+  q_count -= nd;
+  __syncwarp();
+}
+
+template <int R>
+__global__ void __launch_bounds__(256) parse_kernel(ParseParams p, int vh_len) {
+  extern __shared__ __align__(16) uint8_t s_raw[];
+  const uint32_t lane = lane_id();
+  const int warp = threadIdx.x >> 5, n_warps_cta = blockDim.x >> 5;
+  // per warp: packed bases [NW][32] u32, quality bits [NQ][32] u32, window maxima [vh_len][32] u64, queue
+  const size_t per_warp = (size_t)(NW + NQ) * 32 * 4 + (size_t)vh_len * 32 * 8 + sizeof(WarpQueue);
+  uint8_t *base_ptr = s_raw + warp * per_warp;
+  uint64_t *s_vh = reinterpret_cast<uint64_t *>(base_ptr);
+  WarpQueue &Q = *reinterpret_cast<WarpQueue *>(base_ptr + (size_t)vh_len * 32 * 8);
+  uint32_t *s_w = reinterpret_cast<uint32_t *>(base_ptr + (size_t)vh_len * 32 * 8 + sizeof(WarpQueue));
+  uint32_t *s_q = s_w + NW * 32;
+
   const int k = p.k, m = p.m;
   const int w = k - m + 1;                       // minimizer window: m-mers per k-mer
-  const RecordGeom geom = record_geom(R, k);
-  const int max_n = geom.max_kmers;              // counted k-mers per record
-  const uint32_t inv_max_n = 65536u / (uint32_t)max_n + 1u;  // x / max_n for x < 256 (exact: checked on host)
+  const int max_n = record_geom(R, k).max_kmers;  // counted k-mers per record
   const int seg_kmers = SEG - k - 1;             // counted k-mers per segment
   const bool need_ids = p.n_ids > 1;
-  const uint64_t mmask = (m < 32) ? ((1ULL << (2 * m)) - 1ULL) : ~0ULL;
-
-  if (FEWBINS) {
-    sm.resv_base[lane] = ~0ULL;
-    sm.resv_used[lane] = RESV;
-  }
-  __syncwarp();
+  const uint64_t mmask = (1ULL << (2 * m)) - 1ULL;  // m <= 28
+  const uint32_t cut_add = (uint32_t)(32 - p.qual_cutoff) * 0x01010101u;
 
   unsigned long long n_counted = 0, n_records = 0, n_raw = 0;
-  const uint64_t warp_global = (uint64_t)blockIdx.x * WARPS + warp;
-  const uint64_t n_warps = (uint64_t)gridDim.x * WARPS;
+  uint32_t q_head = 0, q_count = 0;
+  const uint64_t warp_global = (uint64_t)blockIdx.x * n_warps_cta + warp;
+  const uint64_t n_warps = (uint64_t)gridDim.x * n_warps_cta;
+  const uint64_t n_sel = (p.n_reads + p.read_stride - 1) / p.read_stride;  // reads this launch looks at
 
-  for (uint64_t ridx = warp_global * p.read_stride; ridx < p.n_reads; ridx += n_warps * p.read_stride) {
-    const int L = p.lens[ridx];
-    if (L < k) continue;  // kcount.cpp:78
-    if (lane == 0) n_raw += L - k + 1;
-    const int nk = L - k - 1;  // counted (interior) k-mers: kcount_cpu.cpp:86
-    if (nk <= 0) continue;
-    if (lane == 0) n_counted += nk;
-    const uint8_t *rd = p.bytes + p.offsets[ridx];
-
-    for (int j0 = 0; j0 < nk; j0 += seg_kmers) {
-      const int nks = min(seg_kmers, nk - j0);  // counted k-mers in this segment
-      const int nb = nks + k + 1;               // bases [j0, j0 + nb)
-      const int nchunks = (nb + 31) >> 5;
-      // ---- (1) parse + pack: bytes -> 2-bit words + quality plane
-      for (int c = 0; c < nchunks; c++) {
-        int pos = 32 * c + (int)lane;
-        uint32_t code = 0, hq = 0;
-        if (pos < nb) {
-          uint32_t b = rd[j0 + pos];
-          code = b & 7u;
-          hq = ((int)(b >> 3) >= p.qual_cutoff) ? 1u : 0u;  // kcount.cpp:81
-          if (code >= 4u) {                                // N: G inside k-mers, never a counted extension
-            code = 2u;
-            hq = 0u;
-          }
-        }
-        uint32_t lo = __brev(__ballot_sync(0xffffffffu, code & 1u));
-        uint32_t hi = __brev(__ballot_sync(0xffffffffu, code & 2u));
-        uint32_t qq = __brev(__ballot_sync(0xffffffffu, hq));
-        if (lane == 0) {
-          sm.W[c] = (spread32(hi) << 1) | spread32(lo);
-          sm.Q[c] = qq;
-        }
+  for (uint64_t batch = warp_global * 32; batch < n_sel; batch += n_warps * 32) {
+    const uint64_t sel = batch + lane;
+    int nk = 0;
+    const uint8_t *rd = nullptr;
+    if (sel < n_sel) {
+      const uint64_t ridx = sel * p.read_stride;
+      const int L = p.lens[ridx];
+      if (L >= k) {  // kcount.cpp:78
+        n_raw += L - k + 1;
+        nk = max(L - k - 1, 0);  // counted (interior) k-mers: kcount_cpu.cpp:86
+        n_counted += nk;
+        rd = p.bytes + p.offsets[ridx];
       }
-      if (lane < 2) {
-        sm.W[nchunks + lane] = 0;
-        sm.Q[nchunks + lane] = 0;
-      }
-      __syncwarp();
-
-      if (need_ids) {
-        // ---- (2a) canonical m-mer at every position (right aligned; order == the reference's left-aligned order)
-        const int npos = nb - m + 1;
-        for (int pos = lane; pos < npos; pos += 32) {
-          uint64_t f = window64(sm.W, pos) >> (64 - 2 * m);
-          uint64_t r = (revcomp_word(f) >> (64 - 2 * m)) & mmask;
-          sm.C[pos] = f < r ? f : r;
-        }
-        __syncwarp();
-        // ---- (2b) sliding maximum over w positions by doubling: after the loop C[p] = max C0[p .. p + span - 1]
-        int span = 1;
-        while (span * 2 <= w) {
-          for (int base = 0; base < npos; base += 32) {
-            int pos = base + (int)lane;
-            uint64_t a = 0, b = 0;
-            bool ok = pos + 2 * span - 1 < npos;
-            if (ok) {
-              a = sm.C[pos];
-              b = sm.C[pos + span];
-            }
-            __syncwarp();
-            if (ok) sm.C[pos] = a > b ? a : b;
-            __syncwarp();
-          }
-          span *= 2;
-        }
-        // ---- (2c) minimizer -> owner rank and local bin
-        for (int jr = lane; jr < nks; jr += 32) {
-          uint64_t a = sm.C[jr + 1], b = sm.C[jr + 1 + w - span];
-          uint64_t mz = (a > b ? a : b) << (64 - 2 * m);  // left aligned as Kmer::get_minimizer_fast returns it
-          uint64_t h = quick_hash(mz), q;
-          uint32_t owner;
-          fast_divmod(h, p.div_ranks, q, owner);
-          sm.ID[jr] = owner * (p.bins_mask + 1u) + ((uint32_t)q & p.bins_mask);
-        }
-        __syncwarp();
-      }
-
-      // ---- (2d) cut runs of equal id into records
-      int carry_rs = 0;  // first k-mer of the run in progress (segment relative)
-      for (int base = 0; base < nks; base += 32) {
-        const int jr = base + (int)lane;
-        const bool valid = jr < nks;
-        uint32_t myid = 0, previd = 0xffffffffu, nextid = 0xfffffffeu;
-        if (valid) {
-          if (need_ids) {
-            myid = sm.ID[jr];
-            if (jr > 0) previd = sm.ID[jr - 1];
-            if (jr + 1 < nks) nextid = sm.ID[jr + 1];
-          } else {
-            if (jr > 0) previd = 0;
-            if (jr + 1 < nks) nextid = 0;
-          }
-        }
-        const bool is_start = valid && myid != previd;
-        const uint32_t smask = __ballot_sync(0xffffffffu, is_start);
-        const uint32_t below = smask & (0xffffffffu >> (31 - lane));
-        const int rs = below ? base + 31 - __clz(below) : carry_rs;
-        if (smask) carry_rs = base + 31 - __clz(smask);
-        const int in_run = jr - rs;
-        const int piece = (int)(((uint32_t)in_run * inv_max_n) >> 16);  // in_run / max_n
-        const bool is_end = valid && (myid != nextid || in_run + 1 == (piece + 1) * max_n);
-        const uint32_t emask = __ballot_sync(0xffffffffu, is_end);
-        if (is_end) {
-          const int start = rs + piece * max_n;
-          const int n = jr - start + 1;
-          // group the records of this step by destination bin: one cursor update per (warp step, bin)
-          const uint32_t peers = need_ids ? __match_any_sync(emask, myid) : emask;
-          const int leader = __ffs(peers) - 1;
-          const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
-          const uint32_t cnt = __popc(peers);
-          unsigned long long slot0 = 0;
-          if ((int)lane == leader) {
-            if (p.count_only) {
-              atomicAdd(&p.bin_cursor[myid], (unsigned long long)cnt);
-            } else if (FEWBINS) {
-              uint32_t used = sm.resv_used[myid];
-              unsigned long long rb = sm.resv_base[myid];
-              if (used + cnt > RESV) {
-                // retire the old reservation: its unused tail becomes empty records
-                if (rb != ~0ULL)
-                  for (uint32_t u = used; u < RESV; u++)
-                    if (rb + u < p.bin_cap[myid]) write_empty<R>(p.bins, p.bin_base[myid], rb + u);
-                rb = atomicAdd(&p.bin_cursor[myid], (unsigned long long)RESV);
-                sm.resv_base[myid] = rb;
-                used = 0;
-              }
-              sm.resv_used[myid] = used + cnt;
-              slot0 = rb + used;
+    }
+    const int n_seg = (nk + seg_kmers - 1) / seg_kmers;
+    const int max_seg = __reduce_max_sync(0xffffffffu, n_seg);
+    for (int sg = 0; sg < max_seg; sg++) {
+      const int j0 = sg * seg_kmers;
+      const int nks = sg < n_seg ? min(seg_kmers, nk - j0) : 0;  // counted k-mers of this lane's segment
+      const int nb = nks ? nks + k + 1 : 0;                      // bases [j0, j0 + nb)
+      const uint8_t *src = rd + j0;
+      const int lead = nks ? (int)((uintptr_t)src & 15) : 0;
+      // ---- (1) pack: aligned 16-byte chunks -> 32 bits of codes + 16 quality bits
+      {
+        const int nch = nks ? (lead + nb + 15) >> 4 : 0;
+        const int max_ch = __reduce_max_sync(0xffffffffu, nch);
+        const uint4 *a0 = reinterpret_cast<const uint4 *>(src - lead);
+        uint32_t qacc = 0;
+        for (int c = 0; c < max_ch; c++) {
+          if (c < nch) {
+            const uint4 v = __ldg(a0 + c);
+            uint32_t c0, c1, c2, c3, h0, h1, h2, h3;
+            pack4(v.x, cut_add, c0, h0);
+            pack4(v.y, cut_add, c1, h1);
+            pack4(v.z, cut_add, c2, h2);
+            pack4(v.w, cut_add, c3, h3);
+            s_w[c * 32 + lane] = (c0 << 24) | (c1 << 16) | (c2 << 8) | c3;
+            const uint32_t h16 = (h0 << 12) | (h1 << 8) | (h2 << 4) | h3;
+            if (c & 1) {
+              s_q[(c >> 1) * 32 + lane] = qacc | h16;
             } else {
-              slot0 = atomicAdd(&p.bin_cursor[myid], (unsigned long long)cnt);
+              qacc = h16 << 16;
+              s_q[(c >> 1) * 32 + lane] = qacc;
             }
           }
-          slot0 = __shfl_sync(peers, slot0, leader);
-          if (!p.count_only) {
-            const unsigned long long slot = slot0 + rank;
-            if (slot < p.bin_cap[myid])
-              write_record<R>(sm, p.bins + p.bin_base[myid] + slot * R, start, n, k);
-            else
-              p.ctr->err_bins_full = 1u;
-          }
-          n_records++;
         }
       }
+      __syncwarp();
+      // ---- (2) scan
+      if (!need_ids) {
+        // one owner, one bin: the segment is cut into records of max_n k-mers
+        const int n_pieces = (nks + max_n - 1) / max_n;
+        const int max_pieces = __reduce_max_sync(0xffffffffu, n_pieces);
+        for (int r = 0; r < max_pieces; r++) {
+          const bool want = r < n_pieces;
+          const uint32_t mask = __ballot_sync(0xffffffffu, want);
+          if (want) {
+            const uint32_t e = (q_head + q_count + __popc(mask & ((1u << lane) - 1u))) & (QCAP - 1);
+            const int start = r * max_n, n = min(max_n, nks - start);
+            Q.val[e] = 0;
+            Q.meta[e] = lane | ((uint32_t)lead << 5) | ((uint32_t)start << 9) | ((uint32_t)n << 17);
+          }
+          q_count += __popc(mask);
+          if (q_count >= 32) drain<R>(p, s_w, s_q, Q, q_head, q_count, n_records);
+        }
+      } else {
+        const int steps = nks ? nb - 1 : 0;  // the last base is only an extension
+        const int max_steps = __reduce_max_sync(0xffffffffu, steps);
+        uint64_t fw = 0, rc = 0, pref = 0, run_val = 0;
+        uint32_t cw = 0;
+        int t = 0, run_start = 0, run_n = 0;
+        for (int i = 0; i <= max_steps; i++) {
+          bool want = false;
+          int out_start = 0, out_n = 0;
+          uint64_t out_val = 0;
+          if (i < steps) {
+            const int pos = lead + i;
+            if ((pos & 15) == 0 || i == 0) cw = s_w[(pos >> 4) * 32 + lane];
+            const uint64_t b = (cw >> (30 - 2 * (pos & 15))) & 3u;
+            fw = ((fw << 2) | b) & mmask;
+            rc = (rc >> 2) | ((3ULL - b) << (2 * m - 2));
+            if (i >= m - 1) {
+              const uint64_t canon = fw < rc ? fw : rc;
+              pref = (t == 0 || canon > pref) ? canon : pref;
+              s_vh[t * 32 + lane] = canon;
+              if (i >= k - 1) {
+                // k-mer starting at base s = i - k + 1: maximum of the last w canonical m-mers
+                uint64_t wmax = pref;
+                if (t != w - 1) {
+                  const uint64_t suf = s_vh[(t + 1) * 32 + lane];
+                  wmax = suf > pref ? suf : pref;
+                }
+                const int s = i - k + 1;
+                if (s >= 1) {  // s == 0 is the first k-mer of the read (or belongs to the previous segment)
+                  const int jr = s - 1;
+                  if (run_n == 0) {
+                    run_start = jr;
+                    run_val = wmax;
+                    run_n = 1;
+                  } else if (wmax != run_val || run_n == max_n) {
+                    want = true;
+                    out_start = run_start;
+                    out_n = run_n;
+                    out_val = run_val;
+                    run_start = jr;
+                    run_val = wmax;
+                    run_n = 1;
+                  } else {
+                    run_n++;
+                  }
+                }
+              }
+              if (t == w - 1) {
+                // block of w m-mers complete: turn it into suffix maxima for the windows that start inside it
+                uint64_t run = canon;
+                for (int u = w - 2; u >= 0; u--) {
+                  const uint64_t x = s_vh[u * 32 + lane];
+                  run = x > run ? x : run;
+                  s_vh[u * 32 + lane] = run;
+                }
+                t = 0;
+              } else {
+                t++;
+              }
+            }
+          } else if (i == steps && run_n) {  // end of the segment: close the open run
+            want = true;
+            out_start = run_start;
+            out_n = run_n;
+            out_val = run_val;
+            run_n = 0;
+          }
+          const uint32_t mask = __ballot_sync(0xffffffffu, want);
+          if (mask) {
+            if (want) {
+              const uint32_t e = (q_head + q_count + __popc(mask & ((1u << lane) - 1u))) & (QCAP - 1);
+              Q.val[e] = out_val;
+              Q.meta[e] = lane | ((uint32_t)lead << 5) | ((uint32_t)out_start << 9) | ((uint32_t)out_n << 17);
+            }
+            q_count += __popc(mask);
+            if (q_count >= 32) drain<R>(p, s_w, s_q, Q, q_head, q_count, n_records);
+          }
+        }
+      }
+      // the packed words are overwritten by the next segment: everything queued must be written first
+      while (q_count) drain<R>(p, s_w, s_q, Q, q_head, q_count, n_records);
       __syncwarp();
     }
   }
 
-  if (FEWBINS && !p.count_only) {
-    // close this warp's open reservations
-    __syncwarp();
-    if (lane < p.n_ids) {
-      unsigned long long rb = sm.resv_base[lane];
-      if (rb != ~0ULL)
-        for (uint32_t u = sm.resv_used[lane]; u < RESV; u++)
-          if (rb + u < p.bin_cap[lane]) write_empty<R>(p.bins, p.bin_base[lane], rb + u);
-    }
-  }
   // statistics: one atomic per warp
-  for (int o = 16; o > 0; o >>= 1) n_records += __shfl_down_sync(0xffffffffu, n_records, o);
+  for (int o = 16; o > 0; o >>= 1) {
+    n_records += __shfl_down_sync(0xffffffffu, n_records, o);
+    n_counted += __shfl_down_sync(0xffffffffu, n_counted, o);
+    n_raw += __shfl_down_sync(0xffffffffu, n_raw, o);
+  }
   if (lane == 0 && !p.count_only) {
     atomicAdd(&p.ctr->parse_counted, n_counted);
     atomicAdd(&p.ctr->parse_records, n_records);
@@ -265,33 +323,41 @@ __global__ void __launch_bounds__(WARPS * 32) parse_kernel(ParseParams p) {
   }
 }
 
+struct ParseLaunch {
+  int grid, threads, vh_len;
+  size_t smem;
+};
+
+static ParseLaunch parse_launch_config(const ParseParams &p, int sm_count) {
+  ParseLaunch L;
+  L.vh_len = p.n_ids > 1 ? (p.k - p.m + 1) : 1;
+  const size_t per_warp = (size_t)(NW + NQ) * 32 * 4 + (size_t)L.vh_len * 32 * 8 + sizeof(WarpQueue);
+  int warps = per_warp * 8 <= 100 * 1024 ? 8 : 4;
+  L.threads = warps * 32;
+  L.smem = per_warp * warps;
+  int per_sm = (int)((220 * 1024) / (L.smem + 1024));
+  per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
+  const uint64_t n_sel = (p.n_reads + p.read_stride - 1) / p.read_stride;
+  uint64_t blocks = (n_sel + (uint64_t)warps * 32 - 1) / ((uint64_t)warps * 32);
+  const uint64_t cap = (uint64_t)sm_count * per_sm;
+  L.grid = (int)(blocks < cap ? (blocks ? blocks : 1) : cap);
+  return L;
+}
+
 template <int R>
-static cudaError_t launch_parse_r(const ParseParams &p, int grid, cudaStream_t s) {
-  if (p.n_ids <= 32)
-    parse_kernel<R, true><<<grid, WARPS * 32, 0, s>>>(p);
-  else
-    parse_kernel<R, false><<<grid, WARPS * 32, 0, s>>>(p);
+static cudaError_t launch_parse_r(const ParseParams &p, int sm_count, cudaStream_t s) {
+  const ParseLaunch L = parse_launch_config(p, sm_count);
+  cudaFuncSetAttribute(parse_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem);
+  parse_kernel<R><<<L.grid, L.threads, L.smem, s>>>(p, L.vh_len);
   return cudaGetLastError();
 }
 
-int parse_grid_size(uint64_t n_reads, uint32_t read_stride, int sm_count) {
-  uint64_t reads = (n_reads + read_stride - 1) / read_stride;
-  uint64_t blocks = (reads + WARPS * 4 - 1) / (WARPS * 4);  // >= 4 reads per warp
-  uint64_t cap = (uint64_t)sm_count * 8;                    // 8 resident CTAs of 256 threads per SM
-  if (blocks > cap) blocks = cap;
-  if (blocks < 1) blocks = 1;
-  return (int)blocks;
-}
-int parse_resv_records() { return RESV; }
-int parse_warps_per_block() { return WARPS; }
-
 cudaError_t launch_parse(const ParseParams &p, int sm_count, cudaStream_t s, uint64_t *launches) {
-  int grid = parse_grid_size(p.n_reads, p.read_stride, sm_count);
   (*launches)++;
   switch (p.rec_bytes) {
-    case 16: return launch_parse_r<16>(p, grid, s);
-    case 32: return launch_parse_r<32>(p, grid, s);
-    case 64: return launch_parse_r<64>(p, grid, s);
+    case 16: return launch_parse_r<16>(p, sm_count, s);
+    case 32: return launch_parse_r<32>(p, sm_count, s);
+    case 64: return launch_parse_r<64>(p, sm_count, s);
   }
   return cudaErrorInvalidValue;
 }
