@@ -237,7 +237,7 @@ __device__ __forceinline__ bool apply_occurrence(const InsertParams &p, const Re
 }
 
 template <int N, int MODE, bool MERGE>
-__global__ void __launch_bounds__(THREADS) insert_kernel(InsertParams p) {
+__global__ void __launch_bounds__(THREADS, 4) insert_kernel(InsertParams p) {
   extern __shared__ __align__(16) uint32_t s_all[];
   const uint32_t lane = lane_id();
   const int warp = threadIdx.x >> 5;
@@ -333,66 +333,83 @@ __global__ void __launch_bounds__(THREADS) insert_kernel(InsertParams p) {
     }
     Occurrence<N> pend;
     uint32_t pend_cnt = 0;
+    bool done = !(q < qend);
     while (true) {
-      const bool have = q < qend;
-      Occurrence<N> cur;
-      if (have) {
-        if (fresh) {  // k-mer j of the record: bases [j+1, j+k], extensions at j and j+k+1
+      // warp-uniform exit; the vote also brings the lanes back together after the divergent probe loops of the
+      // previous step, so that the table loads / REDs below are issued for (almost) all 32 lanes at once
+      if (__all_sync(0xffffffffu, done)) break;
+      if (!done) {
+        const bool have = q < qend;
+        Occurrence<N> cur;
+        if (have) {
+          if (fresh) {  // k-mer j of the record: bases [j+1, j+k], extensions at j and j+k+1
 #pragma unroll
-          for (int i = 0; i < N; i++) fw[i] = rec_window64(rec, j + 1 + 32 * i);
-          fw[N - 1] &= last_mask;
-          revcomp_key<N>(fw, k, rc);
-          fresh = false;
+            for (int i = 0; i < N; i++) fw[i] = rec_window64(rec, j + 1 + 32 * i);
+            fw[N - 1] &= last_mask;
+            revcomp_key<N>(fw, k, rc);
+            fresh = false;
+          }
+          const uint32_t lb = rec_base(rec, j), lq = rec_hq(rec, nbw, j);
+          const uint32_t rb = rec_base(rec, j + k + 1), rq = rec_hq(rec, nbw, j + k + 1);
+          if (key_less<N>(rc, fw)) {  // kcount_cpu.cpp:328-333: swap and complement the extensions
+#pragma unroll
+            for (int i = 0; i < N; i++) cur.key[i] = rc[i];
+            cur.l = rq ? (int)(3u - rb) : -1;
+            cur.r = lq ? (int)(3u - lb) : -1;
+          } else {
+#pragma unroll
+            for (int i = 0; i < N; i++) cur.key[i] = fw[i];
+            cur.l = lq ? (int)lb : -1;
+            cur.r = rq ? (int)rb : -1;
+          }
         }
-        const uint32_t lb = rec_base(rec, j), lq = rec_hq(rec, nbw, j);
-        const uint32_t rb = rec_base(rec, j + k + 1), rq = rec_hq(rec, nbw, j + k + 1);
-        if (key_less<N>(rc, fw)) {  // kcount_cpu.cpp:328-333: swap and complement the extensions
+        bool same = false;
+        if (MERGE && have && pend_cnt) {
+          same = cur.l == pend.l && cur.r == pend.r;
 #pragma unroll
-          for (int i = 0; i < N; i++) cur.key[i] = rc[i];
-          cur.l = rq ? (int)(3u - rb) : -1;
-          cur.r = lq ? (int)(3u - lb) : -1;
+          for (int i = 0; i < N; i++) same = same && cur.key[i] == pend.key[i];
+        }
+        bool advance = false;
+        if (same) {
+          pend_cnt++;
+          advance = true;
         } else {
-#pragma unroll
-          for (int i = 0; i < N; i++) cur.key[i] = fw[i];
-          cur.l = lq ? (int)lb : -1;
-          cur.r = rq ? (int)rb : -1;
+          // a false return = the slot's owner has not completed the key yet: same state again next iteration
+          const bool ok = pend_cnt ? apply_occurrence<N, MODE>(p, rg, pend, pend_cnt, n_unique, n_filter_new) : true;
+          if (ok) {
+            if (!have) {
+              done = true;
+            } else {
+              pend = cur;
+              pend_cnt = 1;
+              advance = true;
+            }
+          }
         }
-      }
-      bool same = false;
-      if (MERGE && have && pend_cnt) {
-        same = cur.l == pend.l && cur.r == pend.r;
+        if (advance) {
+          // ---- next occurrence of the run
+          q++;
+          j++;
+          if (q < qend) {
+            if (j == n) {  // next non-empty record
+              do {
+                rec_i++;
+                rec += W;
+                n = rec[W - 1] & 0xffffu;
+              } while (n == 0);
+              j = 0;
+              fresh = true;
+            } else {  // roll: base j+k enters, base j leaves
+              const uint64_t b = rec_base(rec, j + k);
 #pragma unroll
-        for (int i = 0; i < N; i++) same = same && cur.key[i] == pend.key[i];
-      }
-      if (same) {
-        pend_cnt++;
-      } else {
-        if (pend_cnt && !apply_occurrence<N, MODE>(p, rg, pend, pend_cnt, n_unique, n_filter_new)) continue;  // retry
-        if (!have) break;
-        pend = cur;
-        pend_cnt = 1;
-      }
-      // ---- advance to the next occurrence of the run
-      q++;
-      j++;
-      if (q < qend) {
-        if (j == n) {  // next non-empty record
-          do {
-            rec_i++;
-            rec += W;
-            n = rec[W - 1] & 0xffffu;
-          } while (n == 0);
-          j = 0;
-          fresh = true;
-        } else {  // roll: base j+k enters, base j leaves
-          const uint64_t b = rec_base(rec, j + k);
+              for (int i = 0; i < N - 1; i++) fw[i] = (fw[i] << 2) | (fw[i + 1] >> 62);
+              fw[N - 1] = (fw[N - 1] << 2) | (b << tail);
 #pragma unroll
-          for (int i = 0; i < N - 1; i++) fw[i] = (fw[i] << 2) | (fw[i + 1] >> 62);
-          fw[N - 1] = (fw[N - 1] << 2) | (b << tail);
-#pragma unroll
-          for (int i = N - 1; i > 0; i--) rc[i] = (rc[i] >> 2) | (rc[i - 1] << 62);
-          rc[0] = (rc[0] >> 2) | ((3ULL - b) << 62);
-          rc[N - 1] &= last_mask;
+              for (int i = N - 1; i > 0; i--) rc[i] = (rc[i] >> 2) | (rc[i - 1] << 62);
+              rc[0] = (rc[0] >> 2) | ((3ULL - b) << 62);
+              rc[N - 1] &= last_mask;
+            }
+          }
         }
       }
     }
