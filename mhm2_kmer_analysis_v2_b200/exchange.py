@@ -31,10 +31,31 @@ def _is_cuda_stage(stage):
 def exchange_sizes(send_sizes, group=None, device="cpu"):
     """all-to-all of one u64 per pair: recv[s] = what rank s will send me."""
     world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    # all-gather of the G x G size matrix (works on nccl and gloo alike; G*G*8 bytes)
     t_send = torch.as_tensor(np.asarray(send_sizes, np.int64), device=device)
-    t_recv = torch.empty(world, dtype=torch.int64, device=device)
-    dist.all_to_all_single(t_recv, t_send, group=group)
-    return t_recv.cpu().numpy().astype(np.uint64)
+    rows = [torch.empty(world, dtype=torch.int64, device=device) for _ in range(world)]
+    dist.all_gather(rows, t_send, group=group)
+    return torch.stack(rows)[:, rank].cpu().numpy().astype(np.uint64)
+
+
+def _all_to_all(recvs, sends, group=None):
+    """Variable-size all-to-all. NCCL: one grouped ncclSend/ncclRecv all-to-all; gloo (CPU tests) has no alltoall, so
+    the same exchange is posted as non-blocking point-to-point pairs."""
+    if dist.get_backend(group) == "nccl":
+        dist.all_to_all(recvs, sends, group=group)
+        return
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    reqs = []
+    for peer in range(world):
+        if peer == rank:
+            continue
+        if recvs[peer].numel():
+            reqs.append(dist.irecv(recvs[peer], src=dist.get_global_rank(group, peer) if group else peer, group=group))
+        if sends[peer].numel():
+            reqs.append(dist.isend(sends[peer], dst=dist.get_global_rank(group, peer) if group else peer, group=group))
+    for r in reqs:
+        r.wait()
 
 
 def exchange_supermers(stage, group=None):
@@ -56,7 +77,7 @@ def exchange_supermers(stage, group=None):
         recvs = [device_bytes(recv_ptr + int(recv_off[s]), int(recv_sizes[s]), dev) for s in range(world)]
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        dist.all_to_all(recvs, sends, group=group)
+        _all_to_all(recvs, sends, group=group)
         e1.record()
         torch.cuda.synchronize()
         secs = e0.elapsed_time(e1) / 1e3
@@ -66,7 +87,7 @@ def exchange_supermers(stage, group=None):
         sends = [stage.send_view(d) for d in range(world)]
         recvs = [stage.recv_view(s) for s in range(world)]
         t0 = time.perf_counter()
-        dist.all_to_all(recvs, sends, group=group)
+        _all_to_all(recvs, sends, group=group)
         secs = time.perf_counter() - t0
     stage.exchange_done()
     return int(send_sizes.sum()), int(recv_sizes.sum()), secs
