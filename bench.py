@@ -380,7 +380,9 @@ def main():
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "phases_ms_per_step": {kk: (v / args.steps if kk != "exchange_s" else v / args.steps * 1e3) for kk, v in phase.items()},
             "table": {"unique_kmers": int(g["unique_kmers"]), "final_kmers": int(g["final_kmers"]), "sum_counts": int(g["sum_counts"]),
-                      "table_bytes": int(g["table_bytes"]), "supermer_bytes": int(g["supermer_bytes_out"])},
+                      "table_bytes": int(g["table_bytes"]), "supermer_bytes": int(g["supermer_bytes_out"]),
+                      "local_bins": int(stats["local_bins"]), "split_passes": int(stats["split_passes"]),
+                      "result_bytes": int(stats["result_bytes"])},
             "read_gen_s": t_gen,
         }
         if world > 1:

@@ -78,14 +78,17 @@ typedef struct {
   double base_error_rate;    /* BASE_ERROR_RATE = 0.005 */
   uint64_t table_slots;      /* 0 = reference sizing rule (kcount_cpu.cpp:428-470); else exact slot count */
   uint64_t mem_budget_bytes; /* 0 = 80 % of free device memory */
-  uint32_t local_bins;       /* sub-bins per owner (power of two); 0 = automatic */
+  uint32_t local_bins;       /* sub-bins per owner; 0 = automatic. Multi-rank: must be equal on all ranks (automatic is, when
+                                est_kmers is equal on all ranks or 0). HBM-table mode: power of two */
   uint32_t record_bytes;     /* supermer record size 16/32/64; 0 = automatic */
   uint32_t flags;            /* KC_FLAG_* */
   uint32_t reserved[7];
 } kc_config;
 
 #define KC_FLAG_KEEP_EXT_COUNTS 1u /* finalize also keeps the 8 extension counters + X/F entries (dump D2) */
-#define KC_FLAG_NO_WARP_DEDUP 2u   /* disable __match_any_sync merging of equal k-mers inside a warp */
+#define KC_FLAG_NO_WARP_DEDUP 2u   /* disable the merging of equal consecutive k-mer occurrences before a table update */
+#define KC_FLAG_GLOBAL_TABLE 4u    /* count in one open-addressing table in HBM (the layout use_filter needs) instead of the
+                                      default bin-resident shared-memory tables */
 
 /* Counters the reference logs (SURVEY.md section 5 "Metrics") plus what the roofline needs. */
 typedef struct {
@@ -116,6 +119,9 @@ typedef struct {
   double ms_insert_kernel;     /* insert kernel (both passes when the filter is on), without table clearing / planning */
   double ms_table_clear;       /* zeroing of table, filter and side table before the insert */
   uint64_t insert_kernel_launches; /* launches covered by ms_insert_kernel */
+  uint64_t local_bins;         /* sub-bins per owner actually used */
+  uint64_t split_passes;       /* bin-resident mode: extra passes over bins whose distinct k-mers did not fit shared memory */
+  uint64_t result_bytes;       /* device bytes of the dense result arrays */
 } kc_stats;
 
 /* ---- lifecycle ---------------------------------------------------------------------------------- */

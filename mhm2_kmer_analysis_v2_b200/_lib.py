@@ -14,6 +14,7 @@ KC_ERR_ARG, KC_ERR_CUDA, KC_ERR_NOMEM, KC_ERR_TABLE_FULL, KC_ERR_BINS_FULL, KC_E
 KC_ABI_VERSION = 1
 KC_FLAG_KEEP_EXT_COUNTS = 1
 KC_FLAG_NO_WARP_DEDUP = 2
+KC_FLAG_GLOBAL_TABLE = 4
 
 u8p, u16p, u64p = C.POINTER(C.c_uint8), C.POINTER(C.c_uint16), C.POINTER(C.c_uint64)
 
@@ -36,7 +37,8 @@ class KcStats(C.Structure):
         "max_count", "dropped", "table_slots", "table_bytes", "filter_bytes")] + [
         ("avg_kmer_count", C.c_double), ("ms_parse", C.c_double), ("ms_insert", C.c_double), ("ms_finalize", C.c_double),
         ("kernel_launches", C.c_uint64), ("ms_parse_kernel", C.c_double), ("ms_insert_kernel", C.c_double),
-        ("ms_table_clear", C.c_double), ("insert_kernel_launches", C.c_uint64)]
+        ("ms_table_clear", C.c_double), ("insert_kernel_launches", C.c_uint64), ("local_bins", C.c_uint64),
+        ("split_passes", C.c_uint64), ("result_bytes", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -38,6 +38,9 @@ struct kc_ctx {
   kc_config cfg;
   int k = 0, m = 0, N = 0, rec_bytes = 0, P = 1, G = 1, rank = 0;
   uint32_t n_ids = 1;
+  bool resident = true;       // bin-resident shared-memory counting (kc_count.cu) vs one table in HBM (kc_insert.cu)
+  uint32_t count_slots = 0;   // resident: table slots per CTA
+  uint8_t **d_count_src = nullptr;
   int device = 0, sm_count = 148;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -135,6 +138,60 @@ static int auto_record_bytes(int k, int m, int n_ids) {
   return 64;
 }
 
+
+// Number of local bins, record size and header geometry. Called at creation and again by kc_parse once the amount of
+// input is known (automatic sizing). Everything that depends on n_ids is released when it changes.
+static void configure_bins(kc_ctx *c) {
+  const kc_config &cfg = c->cfg;
+  const double depth = cfg.sequencing_depth > 0 ? cfg.sequencing_depth : 4;
+  const double kmer_err = 1.0 - std::pow(1.0 - cfg.base_error_rate, (double)c->k);
+  uint32_t P = cfg.local_bins;
+  const int R_multi = cfg.record_bytes ? (int)cfg.record_bytes : auto_record_bytes(c->k, c->m, 2);
+  if (!P) {
+    if (c->resident) {
+      // distinct k-mers this rank will own, by the reference's own sizing rule (kmer_dht.cpp:126-131, kcount_cpu.cpp:443-446),
+      // spread over bins whose shared-memory table is then about half full
+      uint64_t est = cfg.est_kmers;
+      if (!est && c->G == 1) est = c->n_bases > c->n_reads * (uint64_t)(c->k - 1) ? c->n_bases - c->n_reads * (uint64_t)(c->k - 1) : 0;
+      if (!est && c->G > 1) {
+        P = 8192;  // no rank-independent estimate: a fixed count keeps the ranks' headers compatible; big bins are split
+      } else {
+        const double distinct = (double)est / depth + (double)est * kmer_err;
+        const double per_bin = 0.55 * count_table_slots(c->N, R_multi);
+        P = (uint32_t)std::min<double>(std::ceil(distinct / per_bin), (double)(1u << 22));
+        if (P < 1) P = 1;
+      }
+    } else {
+      // HBM table: sub-bins keep the table region a bin touches L2-resident once the table is large (measured 2x on C2)
+      uint64_t est = cfg.est_kmers ? cfg.est_kmers : (c->n_bases > c->n_reads * (uint64_t)(c->k - 1) ? c->n_bases - c->n_reads * (uint64_t)(c->k - 1) : 0);
+      const double table_bytes = ((double)est / depth + (cfg.use_filter ? 0.0 : (double)est * kmer_err)) / 0.66 * 36.0;
+      P = table_bytes > 512e6 ? 1024 : 1;
+    }
+  }
+  while ((uint64_t)P * c->G > (1u << 25)) P /= 2;
+  const uint32_t n_ids = P * (uint32_t)c->G;
+  int R = cfg.record_bytes ? (int)cfg.record_bytes : auto_record_bytes(c->k, c->m, (int)n_ids);
+  while (record_geom(R, c->k).max_kmers < 1 && R < 64) R *= 2;
+  if (n_ids != c->n_ids || R != c->rec_bytes || (int)P != c->P) {
+    dev_free(c->d_bin_base);
+    dev_free(c->d_bin_first);
+    dev_free(c->d_bin_cap);
+    dev_free(c->d_cursor);
+    dev_free(c->d_hdr_ptrs);
+    dev_free(c->d_src_ptr);
+    dev_free(c->d_segments);
+    dev_free(c->d_seg_tile_start);
+    dev_free(c->d_regions);
+    dev_free(c->d_total_records);
+    c->caps_valid = false;
+  }
+  c->P = (int)P;
+  c->n_ids = n_ids;
+  c->rec_bytes = R;
+  c->header_bytes = (int)((((uint64_t)P * 8 + kHeaderAlign - 1) / kHeaderAlign) * kHeaderAlign);
+  c->count_slots = c->resident ? count_table_slots(c->N, R) : 0;
+}
+
 // ------------------------------------------------------------------------------------------------ lifecycle
 extern "C" void kc_config_default(kc_config *cfg) {
   memset(cfg, 0, sizeof *cfg);
@@ -174,14 +231,14 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   int m = cfg->m ? (int)cfg->m : reference_minimizer_len(cfg->k);
   if (m > (int)cfg->k) m = cfg->k;
   if (m < 1 || m > 28) return fail(c, KC_ERR_ARG, "kc_create: minimizer length %d unsupported (1..28)", m);
-  uint32_t P = cfg->local_bins ? cfg->local_bins : 1;
-  if (P & (P - 1)) return fail(c, KC_ERR_ARG, "kc_create: local_bins must be a power of two");
-  if ((uint64_t)P * cfg->n_ranks > 65536) return fail(c, KC_ERR_ARG, "kc_create: too many bins");
-  int n_ids = (int)(P * cfg->n_ranks);
-  int R = cfg->record_bytes ? (int)cfg->record_bytes : auto_record_bytes(cfg->k, m, n_ids);
-  if (R != 16 && R != 32 && R != 64) return fail(c, KC_ERR_ARG, "kc_create: record_bytes must be 16, 32 or 64");
-  while (record_geom(R, cfg->k).max_kmers < 1 && R < 64) R *= 2;
-  if (record_geom(R, cfg->k).max_kmers < 1) return fail(c, KC_ERR_ARG, "kc_create: k too large for a 64-byte record");
+  const bool resident = !cfg->use_filter && !(cfg->flags & KC_FLAG_GLOBAL_TABLE);
+  if (!resident && (cfg->local_bins & (cfg->local_bins - 1))) return fail(c, KC_ERR_ARG, "kc_create: local_bins must be a power of two in HBM-table mode");
+  if (cfg->local_bins > (1u << 22) || (uint64_t)std::max(cfg->local_bins, 1u) * cfg->n_ranks > (1u << 25))
+    return fail(c, KC_ERR_ARG, "kc_create: too many bins");
+  if (cfg->record_bytes && cfg->record_bytes != 16 && cfg->record_bytes != 32 && cfg->record_bytes != 64)
+    return fail(c, KC_ERR_ARG, "kc_create: record_bytes must be 16, 32 or 64");
+  if (record_geom(64, cfg->k).max_kmers < 1) return fail(c, KC_ERR_ARG, "kc_create: k too large for a 64-byte record");
+  if (cfg->n_ranks > kCountMaxSrc && resident) return fail(c, KC_ERR_ARG, "kc_create: more than %d ranks", kCountMaxSrc);
 
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -192,11 +249,9 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   c->k = cfg->k;
   c->m = m;
   c->N = (cfg->k + 31) / 32;
-  c->rec_bytes = R;
-  c->P = P;
   c->G = cfg->n_ranks;
   c->rank = cfg->rank;
-  c->n_ids = n_ids;
+  c->resident = resident;
   memset(&c->stats, 0, sizeof c->stats);
   memset(&c->h_ctr, 0, sizeof c->h_ctr);
   int dev = cfg->device;
@@ -222,7 +277,7 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   for (auto &e2 : c->ev_user) cudaEventCreate(&e2);
   if ((e = dev_alloc(&c->d_ctr, 1)) != cudaSuccess) return bail(e, "cudaMalloc");
   cudaMemsetAsync(c->d_ctr, 0, sizeof(DevCounters), c->stream);
-  c->header_bytes = ((c->P * 8 + kHeaderAlign - 1) / kHeaderAlign) * kHeaderAlign;
+  configure_bins(c);
   *out = c;
   return KC_OK;
 }
@@ -264,6 +319,7 @@ extern "C" void kc_destroy(kc_ctx *c) {
   dev_free(c->d_hdr_ptrs);
   dev_free(c->d_recv);
   dev_free(c->d_src_ptr);
+  dev_free(c->d_count_src);
   dev_free(c->d_segments);
   dev_free(c->d_seg_tile_start);
   dev_free(c->d_regions);
@@ -340,7 +396,7 @@ static ParseParams parse_params(kc_ctx *c, const ReadChunk &ch, uint32_t stride,
   p.qual_cutoff = c->cfg.qual_cutoff;
   p.rec_bytes = c->rec_bytes;
   p.n_ids = c->n_ids;
-  p.bins_mask = c->P - 1;
+  p.local_bins = (uint32_t)c->P;
   p.div_ranks = make_fastdiv(c->G);
   p.bins = c->d_bins;
   p.bin_base = c->d_bin_base;
@@ -408,7 +464,14 @@ static int estimate_caps(kc_ctx *c) {
     int rc = layout_bins(c, zero);
     if (rc) return rc;
   }
-  uint32_t stride = (uint32_t)std::max<uint64_t>(1, c->n_reads / 262144);
+  // sample: at least 262144 reads, and about 24 records per bin (a read yields ~2 (L-k-1) / (k-m+2) + 1 of them)
+  uint64_t want_reads = 262144;
+  if (n > 1) {
+    const double avg_len = c->n_reads ? (double)c->n_bases / (double)c->n_reads : 0.0;
+    const double per_read = std::max(1.0, 2.0 * std::max(avg_len - c->k - 1, 0.0) / (double)(c->k - c->m + 2) + 1.0);
+    want_reads = std::max<uint64_t>(want_reads, (uint64_t)(24.0 * n / per_read));
+  }
+  uint32_t stride = (uint32_t)std::max<uint64_t>(1, c->n_reads / want_reads);
   CK(cudaMemsetAsync(c->d_cursor, 0, n * sizeof(unsigned long long), c->stream));
   for (auto &ch : c->chunks) {
     ParseParams p = parse_params(c, ch, stride, 1);
@@ -422,7 +485,7 @@ static int estimate_caps(kc_ctx *c) {
   for (uint32_t i = 0; i < n; i++) {
     double cnt = (double)c->h_cursor[i];
     double est = cnt * stride;
-    if (stride > 1) est += 6.0 * stride * std::sqrt(cnt + 1.0) + 0.02 * est;
+    if (stride > 1) est += 5.0 * stride * std::sqrt(cnt + 1.0) + 0.02 * est;
     cap[i] = (uint64_t)est + pad;
   }
   int rc = layout_bins(c, cap);
@@ -452,6 +515,7 @@ extern "C" int kc_parse(kc_ctx *c) {
   if (!c) return KC_ERR_ARG;
   if (c->chunks.empty()) return fail(c, KC_ERR_STATE, "kc_parse: no reads");
   CK(cudaSetDevice(c->device));
+  if (!c->caps_valid) configure_bins(c);
   CK(cudaEventRecord(c->ev0, c->stream));
   if (!c->caps_valid) {
     int rc = estimate_caps(c);
@@ -638,6 +702,119 @@ static InsertParams insert_params(kc_ctx *c) {
   return ip;
 }
 
+static int alloc_results(kc_ctx *c, ResultSet &r, uint64_t cap, bool with_ext);
+
+// ---- bin-resident counting: one fused kernel does insert + purge + extension resolution + compaction
+static int launch_count_pass(kc_ctx *c) {
+  const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
+  CountParams cp;
+  memset(&cp, 0, sizeof cp);
+  cp.k = c->k;
+  cp.rec_bytes = c->rec_bytes;
+  cp.n_src = c->G;
+  cp.tile_records = insert_tile_records(c->rec_bytes);
+  cp.n_bins = (uint32_t)c->P;
+  cp.header_bytes = c->header_bytes;
+  cp.src_ptr = c->d_count_src;
+  cp.n_slots = c->count_slots;
+  cp.claim_limit = (uint32_t)(0.9 * c->count_slots);
+  cp.dmin_thres = c->cfg.dmin_thres;
+  cp.keep_ext = keep_ext;
+  cp.one_minus_dyn = 1.0 - c->cfg.dyn_min_depth;  // evaluated on the host exactly as the reference's constant expression
+  cp.ctr = c->d_ctr;
+  cp.out_keys = c->res_final.keys;
+  cp.out_counts = c->res_final.counts;
+  cp.out_left = c->res_final.left;
+  cp.out_right = c->res_final.right;
+  cp.cap_final = c->res_final.cap;
+  cp.ext_keys = c->res_ext.keys;
+  cp.ext_counts = c->res_ext.counts;
+  cp.ext_ext8 = c->res_ext.ext8;
+  cp.ext_left = c->res_ext.left;
+  cp.ext_right = c->res_ext.right;
+  cp.cap_ext = keep_ext ? c->res_ext.cap : 0;
+  CK(cudaMemsetAsync(c->d_ctr, 0, offsetof(DevCounters, parse_counted), c->stream));
+  CK(cudaEventRecord(c->ev_clr, c->stream));
+  CK(cudaEventRecord(c->ev_ik0, c->stream));
+  CK(launch_count(cp, c->N, !(c->cfg.flags & KC_FLAG_NO_WARP_DEDUP), c->sm_count, c->stream, &c->launches));
+  CK(cudaEventRecord(c->ev_ik1, c->stream));
+  return KC_OK;
+}
+
+static int insert_resident(kc_ctx *c, const std::vector<uint8_t *> &src) {
+  const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
+  if (!c->d_count_src) CK(dev_alloc(&c->d_count_src, kCountMaxSrc));
+  CK(cudaMemcpyAsync(c->d_count_src, src.data(), c->G * sizeof(uint8_t *), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  // result capacity: an entry that is written has count >= 2, so occurrences / 2 bounds it; the occurrences this owner
+  // receives are estimated from the local parse (the exchange is balanced by the minimizer hash). If the estimate or
+  // the memory budget falls short the kernel reports the exact need and kc_finalize re-runs it.
+  uint64_t occ = std::max<uint64_t>(c->h_ctr.parse_counted, 1024);
+  if (c->G > 1) occ += occ / 4;
+  uint64_t cap = occ / 2 + 1024;
+  size_t free_b = 0, total_b = 0;
+  CK(cudaMemGetInfo(&free_b, &total_b));
+  const uint64_t per_entry = (uint64_t)c->N * 8 + 4 + (keep_ext ? (uint64_t)c->N * 8 + 20 : 0);
+  const uint64_t have = (c->res_final.cap * ((uint64_t)c->N * 8 + 4)) + (c->res_ext.cap * ((uint64_t)c->N * 8 + 20));
+  const uint64_t budget = c->cfg.mem_budget_bytes ? c->cfg.mem_budget_bytes : (uint64_t)((free_b + have) * 0.7);
+  if (cap * per_entry > budget) cap = std::max<uint64_t>(budget / per_entry, 1024);
+  if (c->res_final.cap < cap || !c->res_final.keys) {
+    int rc = alloc_results(c, c->res_final, cap, false);
+    if (rc) return rc;
+  }
+  if (keep_ext && (c->res_ext.cap < cap || !c->res_ext.ext8)) {
+    int rc = alloc_results(c, c->res_ext, cap, true);
+    if (rc) return rc;
+  }
+  CK(cudaEventRecord(c->ev0, c->stream));
+  c->stats.insert_kernel_launches = 1;
+  int rc = launch_count_pass(c);
+  if (rc) return rc;
+  CK(cudaEventRecord(c->ev1, c->stream));
+  c->phase = PH_INSERTED;
+  c->res_final.n = c->res_ext.n = 0;
+  c->res_final.sorted = c->res_ext.sorted = false;
+  return KC_OK;
+}
+
+static void fill_stats(kc_ctx *c);
+
+static int finalize_resident(kc_ctx *c, kc_stats *stats) {
+  const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
+  CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+  c->stats.ms_insert = ms;
+  cudaEventElapsedTime(&ms, c->ev_ik0, c->ev_ik1);
+  c->stats.ms_insert_kernel = ms;
+  c->stats.ms_table_clear = 0;
+  c->stats.ms_finalize = 0;
+  if (c->h_ctr.err_result_full) {
+    // the dense result was under-sized: the counters hold the exact need, allocate that and count again
+    CK(cudaEventRecord(c->ev0, c->stream));
+    int rc = alloc_results(c, c->res_final, c->h_ctr.n_final, false);
+    if (rc) return rc;
+    if (keep_ext && (rc = alloc_results(c, c->res_ext, c->h_ctr.n_ext, true))) return rc;
+    if ((rc = launch_count_pass(c))) return rc;
+    c->stats.insert_kernel_launches++;
+    CK(cudaEventRecord(c->ev1, c->stream));
+    CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->stats.ms_finalize = ms;  // the repeated pass is charged to finalize
+    if (c->h_ctr.err_result_full) return fail(c, KC_ERR_STATE, "finalize: result overflow after exact re-allocation");
+  }
+  if (c->h_ctr.err_count_stack)
+    return fail(c, KC_ERR_TABLE_FULL, "bin-resident counting: a bin could not be split far enough (use more local_bins or KC_FLAG_GLOBAL_TABLE)");
+  c->res_final.n = c->h_ctr.n_final;
+  c->res_ext.n = keep_ext ? c->h_ctr.n_ext : 0;
+  fill_stats(c);
+  c->phase = PH_FINALIZED;
+  if (stats) *stats = c->stats;
+  return KC_OK;
+}
+
 extern "C" int kc_insert(kc_ctx *c) {
   if (!c) return KC_ERR_ARG;
   CK(cudaSetDevice(c->device));
@@ -646,6 +823,14 @@ extern "C" int kc_insert(kc_ctx *c) {
   } else if (c->phase != PH_RECV_READY && c->phase != PH_INSERTED && c->phase != PH_FINALIZED) {
     return fail(c, KC_ERR_STATE, "kc_insert: exchange not completed (kc_exchange_done)");
   }
+  std::vector<uint8_t *> src(c->G, nullptr);
+  for (int s = 0; s < c->G; s++) {
+    if (s == c->rank)
+      src[s] = c->d_bins + c->h_region_off[c->rank];
+    else
+      src[s] = c->recv_bytes[s] ? c->d_recv + c->recv_off[s] : nullptr;
+  }
+  if (c->resident) return insert_resident(c, src);
   int rc = ensure_table(c);
   if (rc) return rc;
   const int n_seg = c->P * c->G;
@@ -655,13 +840,6 @@ extern "C" int kc_insert(kc_ctx *c) {
     CK(dev_alloc(&c->d_seg_tile_start, n_seg + 1));
     CK(dev_alloc(&c->d_regions, c->P));
     CK(dev_alloc(&c->d_total_records, 1));
-  }
-  std::vector<uint8_t *> src(c->G, nullptr);
-  for (int s = 0; s < c->G; s++) {
-    if (s == c->rank)
-      src[s] = c->d_bins + c->h_region_off[c->rank];
-    else
-      src[s] = c->recv_bytes[s] ? c->d_recv + c->recv_off[s] : nullptr;
   }
   CK(cudaMemcpyAsync(c->d_src_ptr, src.data(), c->G * sizeof(uint8_t *), cudaMemcpyHostToDevice, c->stream));
   CK(cudaStreamSynchronize(c->stream));
@@ -739,9 +917,12 @@ static void fill_stats(kc_ctx *c) {
   s.sum_counts = h.sum_counts;
   s.max_count = h.max_count;
   s.dropped = 0;
-  s.table_slots = c->table_slots;
-  s.table_bytes = c->table_slots * slot_bytes(c->N);
-  s.filter_bytes = c->filter_buckets * 32;
+  s.table_slots = c->resident ? c->count_slots : c->table_slots;
+  s.table_bytes = c->resident ? 0 : c->table_slots * slot_bytes(c->N);
+  s.filter_bytes = c->resident ? 0 : c->filter_buckets * 32;
+  s.local_bins = (uint64_t)c->P;
+  s.split_passes = h.split_passes;
+  s.result_bytes = c->res_final.cap * ((uint64_t)c->N * 8 + 4) + (c->res_ext.ext8 ? c->res_ext.cap * ((uint64_t)c->N * 8 + 20) : 0);
   s.avg_kmer_count = h.n_final ? (double)h.sum_counts / (double)h.n_final : 0.0;
   s.kernel_launches = c->launches;
 }
@@ -750,6 +931,7 @@ extern "C" int kc_finalize(kc_ctx *c, kc_stats *stats) {
   if (!c) return KC_ERR_ARG;
   if (c->phase != PH_INSERTED) return fail(c, KC_ERR_STATE, "kc_finalize: call kc_insert first");
   CK(cudaSetDevice(c->device));
+  if (c->resident) return finalize_resident(c, stats);
   CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   float ms = 0;

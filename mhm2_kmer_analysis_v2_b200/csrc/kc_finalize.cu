@@ -14,27 +14,6 @@
 
 namespace kc {
 
-// ExtCounts::get_ext (kcount_cpu.cpp:173-182) on counters A,C,G,T; ties in the sort go to the higher letter (:137-143)
-__device__ __forceinline__ char resolve_ext(const uint32_t c[4], uint32_t count, int dmin_thres, double one_minus_dyn) {
-  int bi = 0;
-  uint32_t top = c[0];
-#pragma unroll
-  for (int b = 1; b < 4; b++)
-    if (c[b] >= top) {
-      top = c[b];
-      bi = b;
-    }
-  uint32_t runner = 0;
-#pragma unroll
-  for (int b = 0; b < 4; b++)
-    if (b != bi && c[b] > runner) runner = c[b];
-  int dmin_dyn = (int)__dmul_rn(one_minus_dyn, (double)count);  // (int)((1.0 - DYN_MIN_DEPTH) * count), in double
-  if (dmin_dyn < dmin_thres) dmin_dyn = dmin_thres;
-  if ((int)top < dmin_dyn) return 'X';
-  if ((int)runner >= dmin_dyn) return 'F';
-  return "ACGT"[bi];
-}
-
 struct FinalizeArgs {
   FinalizeParams p;
   double one_minus_dyn;

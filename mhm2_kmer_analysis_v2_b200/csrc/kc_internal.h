@@ -59,6 +59,9 @@ struct DevCounters {  // device-resident, zeroed by kc_reset
   unsigned long long sum_counts, max_count;
   unsigned long long purged;
   unsigned int err_table_full, err_heavy_full;
+  unsigned int err_result_full;     // bin-resident counting: the dense result arrays were too small (n_final / n_ext hold the need)
+  unsigned int err_count_stack;     // bin-resident counting: a bin could not be split far enough
+  unsigned long long split_passes;  // extra passes over bins whose distinct k-mers did not fit shared memory
   unsigned long long parse_counted, parse_records, parse_raw;
   unsigned int err_bins_full;
 };
@@ -107,7 +110,7 @@ struct ParseParams {
   int count_only;
   int k, m, qual_cutoff, rec_bytes;
   uint32_t n_ids;        // n_ranks * local_bins
-  uint32_t bins_mask;    // local_bins - 1
+  uint32_t local_bins;   // bins per owner: bin = mulhi(mix(hash / n_ranks), local_bins)
   FastDiv div_ranks;
   uint8_t *bins;                     // record storage
   const uint64_t *bin_base;          // [n_ids] first record of each bin
@@ -142,6 +145,35 @@ cudaError_t launch_finalize_heavy(const FinalizeParams &p, uint64_t n_heavy, cud
 int insert_tile_records(int rec_bytes);
 cudaError_t launch_checksum(const uint64_t *keys, const uint16_t *counts, const char *left, const char *right, const uint16_t *ext8,
                             uint64_t n, int n_words, unsigned long long *out, cudaStream_t s, uint64_t *launches);
+
+// ---- bin-resident counting (kc_count.cu) ----------------------------------------
+// The default path: every local bin is small enough that the distinct k-mers of the bin fit a hash table in shared
+// memory; one CTA counts a bin there and emits the purged / extension-resolved entries straight to the dense result.
+static const int kCountMaxSrc = 64;    // source ranks per owner the count kernel can read from
+static const int kCountMaxHeavy = 64;  // keys with more than 65535 occurrences per (bin, split pass)
+
+struct CountParams {
+  int k, rec_bytes, n_src, tile_records;
+  uint32_t n_bins;
+  int header_bytes;                  // bytes of the per-source header block [n_bins x {u32 first_record, u32 n_records}]
+  const uint8_t *const *src_ptr;     // [n_src] region of each source rank for this owner (nullptr = nothing received)
+  uint32_t n_slots;                  // table slots in shared memory
+  uint32_t claim_limit;              // claimed slots at which a pass gives up and the bin is split further
+  int dmin_thres, keep_ext;
+  double one_minus_dyn;
+  DevCounters *ctr;
+  uint64_t *out_keys;
+  uint16_t *out_counts;
+  char *out_left, *out_right;
+  uint64_t cap_final;
+  uint64_t *ext_keys;
+  uint16_t *ext_counts, *ext_ext8;
+  char *ext_left, *ext_right;
+  uint64_t cap_ext;
+};
+// slots that fit the shared-memory budget of one CTA for N key words
+uint32_t count_table_slots(int n_words, int rec_bytes);
+cudaError_t launch_count(const CountParams &p, int n_words, bool merge_runs, int sm_count, cudaStream_t s, uint64_t *launches);
 
 static const int kHeaderAlign = 64;
 

@@ -14,7 +14,7 @@
 //       computed with the block prefix/suffix-maximum scheme (all lanes stay in lock step, no data-dependent loops).
 //       A run of k-mers with the same minimizer (cut to the record capacity) is one supermer.
 //   (3) emit: finished runs go to a small per-warp queue; whenever 32 are queued every lane takes one: owner =
-//       quick_hash(minimizer) % n_ranks (src/kcount/kmer_dht.cpp:193-196), local bin = (hash / n_ranks) & (bins-1), one
+//       quick_hash(minimizer) % n_ranks (src/kcount/kmer_dht.cpp:193-196), local bin = mulhi(mix(hash / n_ranks), bins), one
 //       cursor update per distinct bin in the batch, and the fixed-size record is cut out of the owning lane's packed
 //       words with funnel shifts and written with 128-bit stores into the per-(owner, bin) area of the send buffer.
 #include "kc_internal.h"
@@ -108,7 +108,9 @@ __device__ __forceinline__ void drain(const ParseParams &p, const uint32_t *s_w,
       uint64_t h = quick_hash(mz), q;
       uint32_t owner;
       fast_divmod(h, p.div_ranks, q, owner);
-      id = owner * (p.bins_mask + 1u) + ((uint32_t)q & p.bins_mask);
+      uint32_t x = ((uint32_t)q ^ (uint32_t)(q >> 32)) * 0x9e3779b1u;  // the high bits pick the bin
+      x ^= x >> 15;
+      id = owner * p.local_bins + __umulhi(x * 0x85ebca6bu, p.local_bins);
     }
   }
   // one cursor update per distinct bin of the batch (full-mask collectives: all lanes take part, idle ones stand alone)

@@ -37,7 +37,7 @@ class KcountStage:
 
     def __init__(self, k, m=0, qual_offset=33, qual_cutoff=20, dmin_thres=2, dyn_min_depth=0.9, use_filter=False, rank=0,
                  n_ranks=1, device=-1, est_kmers=0, sequencing_depth=4, base_error_rate=0.005, table_slots=0,
-                 mem_budget_bytes=0, local_bins=0, record_bytes=0, keep_ext_counts=False, warp_dedup=True):
+                 mem_budget_bytes=0, local_bins=0, record_bytes=0, keep_ext_counts=False, warp_dedup=True, global_table=False):
         self.L = _lib.lib()
         cfg = _lib.KcConfig()
         self.L.kc_config_default(C.byref(cfg))
@@ -45,7 +45,8 @@ class KcountStage:
         cfg.dyn_min_depth, cfg.use_filter, cfg.rank, cfg.n_ranks, cfg.device = dyn_min_depth, int(use_filter), rank, n_ranks, device
         cfg.est_kmers, cfg.sequencing_depth, cfg.base_error_rate = est_kmers, sequencing_depth, base_error_rate
         cfg.table_slots, cfg.mem_budget_bytes, cfg.local_bins, cfg.record_bytes = table_slots, mem_budget_bytes, local_bins, record_bytes
-        cfg.flags = (_lib.KC_FLAG_KEEP_EXT_COUNTS if keep_ext_counts else 0) | (0 if warp_dedup else _lib.KC_FLAG_NO_WARP_DEDUP)
+        cfg.flags = ((_lib.KC_FLAG_KEEP_EXT_COUNTS if keep_ext_counts else 0) | (0 if warp_dedup else _lib.KC_FLAG_NO_WARP_DEDUP)
+                     | (_lib.KC_FLAG_GLOBAL_TABLE if global_table else 0))
         self.cfg = cfg
         self.h = C.c_void_p()
         rc = self.L.kc_create(C.byref(cfg), C.byref(self.h))
