@@ -28,7 +28,7 @@
 
 namespace kc {
 
-static const int CT_THREADS = 256;
+static const int CT_THREADS = 384;
 static const int CT_WARPS = CT_THREADS / 32;
 static const int CT_STACK = 48;  // pending (split, residue) parts of a bin
 static const uint32_t C_NOT_FOUND = 0xffffffffu;
