@@ -56,8 +56,10 @@ struct kc_ctx {
   uint8_t *d_bins = nullptr;
   uint64_t bins_bytes = 0, bins_alloc = 0;
   int header_bytes = 0;
-  std::vector<uint64_t> h_bin_base, h_bin_first, h_bin_cap, h_region_off, h_region_bytes;
-  std::vector<unsigned long long> h_cursor;
+  std::vector<uint64_t> h_region_off, h_region_bytes;
+  std::vector<unsigned long long> h_owner_used;  // per owner: records up to the end of its last non-empty bin
+  unsigned long long *d_block_sums = nullptr;
+  unsigned long long *d_owner_vals = nullptr;    // [owner_records | region_off (+total) | region_bytes | owner_used]
   uint64_t *d_bin_base = nullptr, *d_bin_first = nullptr, *d_bin_cap = nullptr;
   unsigned long long *d_cursor = nullptr;
   uint8_t **d_hdr_ptrs = nullptr;
@@ -317,6 +319,8 @@ extern "C" void kc_destroy(kc_ctx *c) {
   dev_free(c->d_bin_cap);
   dev_free(c->d_cursor);
   dev_free(c->d_hdr_ptrs);
+  dev_free(c->d_owner_vals);
+  dev_free(c->d_block_sums);
   dev_free(c->d_recv);
   dev_free(c->d_src_ptr);
   dev_free(c->d_count_src);
@@ -406,64 +410,77 @@ static ParseParams parse_params(kc_ctx *c, const ReadChunk &ch, uint32_t stride,
   return p;
 }
 
-// lay the bins out: per owner [header block][bin 0 records][bin 1 records]..., given per-bin capacities in records
-static int layout_bins(kc_ctx *c, const std::vector<uint64_t> &cap) {
+// Lay the bins out on the device: per owner [header block][bin 0 records][bin 1 records]..., capacities from the
+// cursors of a counting pass (stride > 1: a strided sample, scaled with a noise margin; stride == 1: exact). Only the
+// per-owner region offsets / sizes (n_ranks values) come back to the host.
+static int layout_bins(kc_ctx *c, uint32_t stride) {
   const uint32_t n = c->n_ids;
-  c->h_bin_base.assign(n, 0);
-  c->h_bin_first.assign(n, 0);
-  c->h_bin_cap = cap;
+  LayoutParams lp;
+  memset(&lp, 0, sizeof lp);
+  lp.n_ranks = (uint32_t)c->G;
+  lp.local_bins = (uint32_t)c->P;
+  lp.stride = stride;
+  lp.rec_bytes = c->rec_bytes;
+  lp.header_bytes = c->header_bytes;
+  lp.pad = 64;
+  lp.bin_cursor = c->d_cursor;
+  lp.bin_cap = c->d_bin_cap;
+  lp.bin_first = c->d_bin_first;
+  lp.bin_base = c->d_bin_base;
+  lp.owner_records = c->d_owner_vals;
+  lp.region_off = c->d_owner_vals + kCountMaxSrc;
+  lp.region_bytes = c->d_owner_vals + 2 * kCountMaxSrc + 1;
+  lp.block_sums = c->d_block_sums;
+  lp.err_too_large = &c->d_ctr->err_bins_full;  // (checked right below, reset before the real parse)
+  (void)n;
+  CK(cudaMemsetAsync(&c->d_ctr->err_bins_full, 0, sizeof(unsigned int), c->stream));
+  CK(launch_layout(lp, c->stream, &c->launches));
+  std::vector<unsigned long long> h(3 * kCountMaxSrc + 2);
+  unsigned int too_large = 0;
+  CK(cudaMemcpyAsync(h.data(), c->d_owner_vals, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(&too_large, &c->d_ctr->err_bins_full, sizeof too_large, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (too_large) return fail(c, KC_ERR_ARG, "supermer region too large for 32-bit record indices; use more ranks");
   c->h_region_off.assign(c->G, 0);
   c->h_region_bytes.assign(c->G, 0);
-  uint64_t at = 0;
-  std::vector<uint8_t *> hdr(c->G);
   for (int o = 0; o < c->G; o++) {
-    c->h_region_off[o] = at;
-    at += c->header_bytes;
-    uint64_t first = 0;
-    for (int b = 0; b < c->P; b++) {
-      uint32_t id = o * c->P + b;
-      if (first + cap[id] > 0xffffffffULL) return fail(c, KC_ERR_ARG, "supermer region too large for 32-bit record index; use more local bins/ranks");
-      c->h_bin_first[id] = first;
-      c->h_bin_base[id] = at + first * c->rec_bytes;
-      first += cap[id];
-    }
-    at += first * c->rec_bytes;
-    at = (at + 255) & ~255ULL;
-    c->h_region_bytes[o] = at - c->h_region_off[o];
+    c->h_region_off[o] = h[kCountMaxSrc + o];
+    c->h_region_bytes[o] = h[2 * kCountMaxSrc + 1 + o];
   }
-  c->bins_bytes = at;
-  if (at > c->bins_alloc) {
+  c->bins_bytes = h[kCountMaxSrc + c->G];
+  if (c->bins_bytes > c->bins_alloc) {
     dev_free(c->d_bins);
-    uint64_t want = at + at / 16;
+    uint64_t want = c->bins_bytes + c->bins_bytes / 16;
     CK(dev_alloc(&c->d_bins, want));
     c->bins_alloc = want;
   }
+  std::vector<uint8_t *> hdr(c->G);
+  for (int o = 0; o < c->G; o++) hdr[o] = c->d_bins + c->h_region_off[o];
+  CK(cudaMemcpyAsync(c->d_hdr_ptrs, hdr.data(), c->G * sizeof(uint8_t *), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));  // hdr is a local
+  return KC_OK;
+}
+
+static int ensure_bin_arrays(kc_ctx *c) {
+  const uint32_t n = c->n_ids;
   if (!c->d_bin_base) {
     CK(dev_alloc(&c->d_bin_base, n));
     CK(dev_alloc(&c->d_bin_first, n));
     CK(dev_alloc(&c->d_bin_cap, n));
     CK(dev_alloc(&c->d_cursor, n));
     CK(dev_alloc(&c->d_hdr_ptrs, c->G));
+    dev_free(c->d_block_sums);
+    CK(dev_alloc(&c->d_block_sums, (uint64_t)c->G * layout_blocks_per_owner((uint32_t)c->P)));
   }
-  for (int o = 0; o < c->G; o++) hdr[o] = c->d_bins + c->h_region_off[o];
-  CK(cudaMemcpyAsync(c->d_bin_base, c->h_bin_base.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(c->d_bin_first, c->h_bin_first.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(c->d_bin_cap, c->h_bin_cap.data(), n * 8, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(c->d_hdr_ptrs, hdr.data(), c->G * sizeof(uint8_t *), cudaMemcpyHostToDevice, c->stream));
-  CK(cudaStreamSynchronize(c->stream));  // host vectors above are reused
+  if (!c->d_owner_vals) CK(dev_alloc(&c->d_owner_vals, 4 * kCountMaxSrc + 4));
   return KC_OK;
 }
-
-static uint64_t reservation_pad(kc_ctx *) { return 64; }
 
 // capacity estimate from a strided sample of the reads (count-only run of the parse kernel)
 static int estimate_caps(kc_ctx *c) {
   const uint32_t n = c->n_ids;
-  if (!c->d_cursor) {
-    std::vector<uint64_t> zero(n, 0);
-    int rc = layout_bins(c, zero);
-    if (rc) return rc;
-  }
+  int rc = ensure_bin_arrays(c);
+  if (rc) return rc;
   // sample: at least 262144 reads, and about 24 records per bin (a read yields ~2 (L-k-1) / (k-m+2) + 1 of them)
   uint64_t want_reads = 262144;
   if (n > 1) {
@@ -477,18 +494,7 @@ static int estimate_caps(kc_ctx *c) {
     ParseParams p = parse_params(c, ch, stride, 1);
     CK(launch_parse(p, c->sm_count, c->stream, &c->launches));
   }
-  c->h_cursor.assign(n, 0);
-  CK(cudaMemcpyAsync(c->h_cursor.data(), c->d_cursor, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
-  std::vector<uint64_t> cap(n);
-  const uint64_t pad = reservation_pad(c);
-  for (uint32_t i = 0; i < n; i++) {
-    double cnt = (double)c->h_cursor[i];
-    double est = cnt * stride;
-    if (stride > 1) est += 5.0 * stride * std::sqrt(cnt + 1.0) + 0.02 * est;
-    cap[i] = (uint64_t)est + pad;
-  }
-  int rc = layout_bins(c, cap);
+  rc = layout_bins(c, stride);
   if (rc) return rc;
   c->caps_valid = true;
   return KC_OK;
@@ -496,7 +502,9 @@ static int estimate_caps(kc_ctx *c) {
 
 static int run_parse(kc_ctx *c) {
   const uint32_t n = c->n_ids;
+  unsigned long long *owner_used = c->d_owner_vals + 3 * kCountMaxSrc + 2;
   CK(cudaMemsetAsync(c->d_cursor, 0, n * sizeof(unsigned long long), c->stream));
+  CK(cudaMemsetAsync(owner_used, 0, kCountMaxSrc * sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(&c->d_ctr->parse_counted, 0, 3 * sizeof(unsigned long long) + sizeof(unsigned int), c->stream));
   CK(cudaEventRecord(c->ev_pk0, c->stream));
   for (auto &ch : c->chunks) {
@@ -504,9 +512,9 @@ static int run_parse(kc_ctx *c) {
     CK(launch_parse(p, c->sm_count, c->stream, &c->launches));
   }
   CK(cudaEventRecord(c->ev_pk1, c->stream));
-  CK(launch_write_headers(c->d_hdr_ptrs, c->d_bin_first, c->d_cursor, c->d_bin_cap, c->G, c->P, c->stream, &c->launches));
-  c->h_cursor.assign(n, 0);
-  CK(cudaMemcpyAsync(c->h_cursor.data(), c->d_cursor, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  CK(launch_write_headers(c->d_hdr_ptrs, c->d_bin_first, c->d_cursor, c->d_bin_cap, c->G, c->P, owner_used, c->stream, &c->launches));
+  c->h_owner_used.assign(kCountMaxSrc, 0);
+  CK(cudaMemcpyAsync(c->h_owner_used.data(), owner_used, kCountMaxSrc * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
   return KC_OK;
 }
@@ -526,10 +534,7 @@ extern "C" int kc_parse(kc_ctx *c) {
   CK(cudaStreamSynchronize(c->stream));
   if (c->h_ctr.err_bins_full) {
     // the sample under-estimated a bin: the cursors now hold the exact demand, lay out again and redo
-    std::vector<uint64_t> cap(c->n_ids);
-    const uint64_t pad = reservation_pad(c);
-    for (uint32_t i = 0; i < c->n_ids; i++) cap[i] = c->h_cursor[i] + pad;
-    rc = layout_bins(c, cap);
+    rc = layout_bins(c, 1);
     if (rc) return rc;
     rc = run_parse(c);
     if (rc) return rc;
@@ -557,13 +562,7 @@ extern "C" int kc_parse(kc_ctx *c) {
 // ------------------------------------------------------------------------------------------------ exchange
 static uint64_t used_region_bytes(kc_ctx *c, int o) {
   // header + records up to the end of the last non-empty bin (the slack behind it need not travel)
-  uint64_t end = 0;
-  for (int b = 0; b < c->P; b++) {
-    uint32_t id = o * c->P + b;
-    uint64_t cnt = std::min<uint64_t>(c->h_cursor[id], c->h_bin_cap[id]);
-    if (cnt) end = std::max(end, c->h_bin_first[id] + cnt);
-  }
-  return c->header_bytes + end * c->rec_bytes;
+  return c->header_bytes + (uint64_t)c->h_owner_used[o] * c->rec_bytes;
 }
 
 extern "C" int kc_exchange_send_sizes(kc_ctx *c, uint64_t *send_bytes) {

@@ -137,7 +137,23 @@ struct PlanParams {
 };
 cudaError_t launch_plan(const PlanParams &p, cudaStream_t s, uint64_t *launches);
 cudaError_t launch_write_headers(uint8_t *const *dst_header, const uint64_t *bin_base, const unsigned long long *bin_cursor,
-                                 const uint64_t *bin_cap, int n_ranks, int local_bins, cudaStream_t s, uint64_t *launches);
+                                 const uint64_t *bin_cap, int n_ranks, int local_bins, unsigned long long *owner_used, cudaStream_t s,
+                                 uint64_t *launches);
+// bin layout computed on the device from the cursors of a (sampled) counting pass
+struct LayoutParams {
+  uint32_t n_ranks, local_bins, stride;
+  int rec_bytes, header_bytes;
+  unsigned long long pad;                 // records added to every bin
+  const unsigned long long *bin_cursor;   // [n_ids] records seen by the counting pass
+  uint64_t *bin_cap, *bin_first, *bin_base;  // [n_ids] out
+  unsigned long long *owner_records;      // [n_ranks] out: record capacity of each owner's area
+  unsigned long long *region_off;         // [n_ranks + 1] out: byte offset of each owner's region, total at the end
+  unsigned long long *region_bytes;       // [n_ranks] out
+  unsigned long long *block_sums;         // [n_ranks * layout_blocks_per_owner(local_bins)] scratch
+  unsigned int *err_too_large;
+};
+inline uint32_t layout_blocks_per_owner(uint32_t local_bins) { return (local_bins + 1023u) / 1024u; }
+cudaError_t launch_layout(const LayoutParams &p, cudaStream_t s, uint64_t *launches);
 cudaError_t launch_insert(const InsertParams &p, int n_words, int mode, bool merge_runs, int sm_count, cudaStream_t s, uint64_t *launches);
 cudaError_t launch_finalize(const FinalizeParams &p, int sm_count, cudaStream_t s, uint64_t *launches);
 // second finalize step for the heavy keys listed by launch_finalize, after the MODE_HEAVY recount

@@ -367,7 +367,7 @@ cudaError_t launch_parse(const ParseParams &p, int sm_count, cudaStream_t s, uin
 // per-destination header blocks: entry b of owner o = {first record of bin (o,b) inside the owner's record area,
 // number of records actually present}
 __global__ void write_headers_kernel(uint8_t *const *dst_header, const uint64_t *bin_first, const unsigned long long *bin_cursor,
-                                     const uint64_t *bin_cap, int n_ranks, int local_bins) {
+                                     const uint64_t *bin_cap, int n_ranks, int local_bins, unsigned long long *owner_used) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_ranks * local_bins) return;
   int o = i / local_bins, b = i % local_bins;
@@ -375,13 +375,96 @@ __global__ void write_headers_kernel(uint8_t *const *dst_header, const uint64_t 
   if (c > bin_cap[i]) c = bin_cap[i];
   uint2 *hdr = reinterpret_cast<uint2 *>(dst_header[o]);
   hdr[b] = make_uint2((uint32_t)bin_first[i], (uint32_t)c);
+  // records up to the end of the last non-empty bin: the slack behind it need not travel in the exchange
+  if (c) atomicMax(owner_used + o, (unsigned long long)bin_first[i] + c);
 }
 
 cudaError_t launch_write_headers(uint8_t *const *dst_header, const uint64_t *bin_first, const unsigned long long *bin_cursor,
-                                 const uint64_t *bin_cap, int n_ranks, int local_bins, cudaStream_t s, uint64_t *launches) {
+                                 const uint64_t *bin_cap, int n_ranks, int local_bins, unsigned long long *owner_used, cudaStream_t s,
+                                 uint64_t *launches) {
   int n = n_ranks * local_bins;
   (*launches)++;
-  write_headers_kernel<<<(n + 255) / 256, 256, 0, s>>>(dst_header, bin_first, bin_cursor, bin_cap, n_ranks, local_bins);
+  write_headers_kernel<<<(n + 255) / 256, 256, 0, s>>>(dst_header, bin_first, bin_cursor, bin_cap, n_ranks, local_bins, owner_used);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ bin layout on the device
+// Capacities from the (sampled or exact) cursors and their exclusive scan -> first record of every bin inside its
+// owner's record area. No per-bin data crosses to the host (there may be millions of bins).
+//   1. caps + scan inside blocks of 1024 bins (grid = blocks per owner x owners), block totals
+//   2. one thread: scan of the block totals per owner, owner totals, region offsets
+//   3. add the block offsets; byte offset of every bin
+__global__ void __launch_bounds__(1024) layout_caps_kernel(LayoutParams p) {
+  __shared__ unsigned long long s_warp[32];
+  const uint32_t o = blockIdx.y, P = p.local_bins;
+  const uint32_t b = blockIdx.x * 1024u + threadIdx.x;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  unsigned long long cap = 0;
+  if (b < P) {
+    const double cnt = (double)p.bin_cursor[o * P + b];
+    double est = cnt * p.stride;
+    if (p.stride > 1) est += 7.0 * p.stride * sqrt(cnt + 1.0) + 0.03 * est;  // sampling noise of a strided sample
+    cap = (unsigned long long)est + p.pad;
+    p.bin_cap[o * P + b] = cap;
+  }
+  unsigned long long incl = cap;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned long long v = __shfl_up_sync(0xffffffffu, incl, d);
+    if ((int)lane >= d) incl += v;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    unsigned long long w = s_warp[lane], wi = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long v = __shfl_up_sync(0xffffffffu, wi, d);
+      if ((int)lane >= d) wi += v;
+    }
+    s_warp[lane] = wi - w;
+    if (lane == 31) p.block_sums[o * gridDim.x + blockIdx.x] = wi;
+  }
+  __syncthreads();
+  if (b < P) p.bin_first[o * P + b] = s_warp[warp] + incl - cap;
+}
+
+__global__ void layout_regions_kernel(LayoutParams p, uint32_t blocks_per_owner) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  unsigned long long at = 0;
+  for (uint32_t o = 0; o < p.n_ranks; o++) {
+    unsigned long long rec = 0;
+    for (uint32_t j = 0; j < blocks_per_owner; j++) {
+      const unsigned long long v = p.block_sums[o * blocks_per_owner + j];
+      p.block_sums[o * blocks_per_owner + j] = rec;
+      rec += v;
+    }
+    p.owner_records[o] = rec;
+    if (rec > 0xffffffffULL) *p.err_too_large = 1u;  // headers carry 32-bit record indices
+    p.region_off[o] = at;
+    at += p.header_bytes + rec * p.rec_bytes;
+    at = (at + 255ULL) & ~255ULL;
+    p.region_bytes[o] = at - p.region_off[o];
+  }
+  p.region_off[p.n_ranks] = at;  // total
+}
+
+__global__ void layout_bases_kernel(LayoutParams p, uint32_t blocks_per_owner) {
+  const uint32_t o = blockIdx.y;
+  const uint32_t b = blockIdx.x * 1024u + threadIdx.x;
+  if (b >= p.local_bins) return;
+  const uint32_t i = o * p.local_bins + b;
+  const unsigned long long first = p.bin_first[i] + p.block_sums[o * blocks_per_owner + blockIdx.x];
+  p.bin_first[i] = first;
+  p.bin_base[i] = p.region_off[o] + p.header_bytes + first * p.rec_bytes;
+}
+
+cudaError_t launch_layout(const LayoutParams &p, cudaStream_t s, uint64_t *launches) {
+  (*launches) += 3;
+  const uint32_t nb = layout_blocks_per_owner(p.local_bins);
+  layout_caps_kernel<<<dim3(nb, p.n_ranks), 1024, 0, s>>>(p);
+  layout_regions_kernel<<<1, 32, 0, s>>>(p, nb);
+  layout_bases_kernel<<<dim3(nb, p.n_ranks), 1024, 0, s>>>(p, nb);
   return cudaGetLastError();
 }
 
