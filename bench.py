@@ -14,8 +14,9 @@ exchange when N > 1 (NCCL all-to-all), table insert (kc_insert), purge/extension
            stage's stream, host gaps included), max over ranks.
   e2e      same stage through the C ABI with HOST buffers: pinned reads -> kc_add_reads (H2D) -> run -> kc_result_copy of
            the final (k-mer, count, left, right) arrays into pinned host memory (D2H); wall clock between device syncs.
-  roofline insert kernel alone: B_alg(k) bytes per counted k-mer x k-mers per launch / its CUDA-event time,
-           against MEASURED_PEAKS.json hbm_gbs.
+  roofline the dominant kernel alone (count_kernel = insert + purge + extension resolution over shared-memory tables;
+           insert_kernel with --filter 1 / --global-table): B_alg(k) ALGORITHMIC bytes per counted k-mer x
+           k-mers per launch / its CUDA-event time, against MEASURED_PEAKS.json hbm_gbs.
   cpu_baseline  the reference's own CPU kcount (oracle/_ref/kcount_ref: its unmodified sources behind a one-node UPC++
            stand-in, one forked rank per host core) on a bounded prefix of the same reads; falls back to the C restatement
            (oracle/libkcount_oracle.so, one thread) when the reference build is not present.
@@ -62,7 +63,7 @@ def config_dict(args, n_gpus):
                     f"0.5% substitutions, seed 2002, k={args.k}, kcount stage only",
         "k": args.k, "reads_per_gpu": args.reads_per_gpu, "read_len": READ_LEN, "n_gpus": n_gpus, "filter": bool(args.filter),
         "dmin_thres": 2, "parallelism": f"owner-partitioned x{n_gpus}" if n_gpus > 1 else "single GPU",
-        "l2": "inputs (reads, supermers, table) each far larger than the 126 MB L2; no explicit flush",
+        "l2": "inputs (reads 3 GB, supermer records 13 GB, result 5 GB per GPU) each far larger than the 126 MB L2; no explicit flush",
     }
 
 
@@ -206,6 +207,7 @@ def main():
     ap.add_argument("--local-bins", type=int, default=0)
     ap.add_argument("--record-bytes", type=int, default=0)
     ap.add_argument("--table-slots", type=int, default=0, help="exact table size in slots (0 = the reference's sizing rule)")
+    ap.add_argument("--global-table", action="store_true", help="count in one HBM table (kc_insert.cu) instead of bin-resident tables")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-sample-reads", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -259,7 +261,8 @@ def main():
     h2d_bytes = len(reads.bytes) + n * 10
 
     st = K.KcountStage(k, rank=rank, n_ranks=world, device=local_rank, est_kmers=raw_local, use_filter=bool(args.filter),
-                       local_bins=args.local_bins, record_bytes=args.record_bytes, table_slots=args.table_slots)
+                       local_bins=args.local_bins, record_bytes=args.record_bytes, table_slots=args.table_slots,
+                       global_table=args.global_table)
 
     def barrier():
         if dist is not None:
@@ -377,7 +380,8 @@ def main():
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic", "config": config_dict(args, world),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                         "kernel": "insert_kernel", "peak_source": peak_src, "b_alg_bytes_per_kmer": b_alg(k),
+                         "kernel": "insert_kernel (HBM table)" if (args.filter or args.global_table) else "count_kernel (bin-resident insert + purge + extension resolution)",
+                         "peak_source": peak_src, "b_alg_bytes_per_kmer": b_alg(k),
                          "kmers_per_launch": inserted, "ms_per_launch": ms_insert_kernel},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "phases_ms_per_step": {kk: (v / args.steps if kk != "exchange_s" else v / args.steps * 1e3) for kk, v in phase.items()},
