@@ -1,0 +1,309 @@
+// kcount_b200.hpp -- header-only C++ façade over the C ABI (kcount_b200.h) with the names, argument order and call
+// sequence of the reference's kcount interface, so that a caller written against the reference compiles against this
+// with a namespace change:
+//
+//   reference (src/contigging.cpp:83-104)                          here
+//   -------------------------------------------------------------  ------------------------------------------------
+//   Kmer<MAX_K>::set_k(k)                                          kcount_b200::Kmer<MAX_K>::set_k(k)
+//   dist_object<KmerDHT<MAX_K>> kmer_dht(world(), my_num_kmers,    kcount_b200::dist_object<KmerDHT<MAX_K>> kmer_dht(
+//       0, max_kmer_store, max_rpcs_in_flight, use_qf, seq_depth)      my_num_kmers, 0, max_kmer_store, max_rpcs, use_qf, seq_depth)
+//   analyze_kmers(k, qual_offset, packed_reads_list, dmin_thres,   kcount_b200::analyze_kmers(k, qual_offset, packed_reads_list,
+//       kmer_dht, dump_kmers)                                          dmin_thres, kmer_dht, dump_kmers)
+//   kmer_dht->get_avg_kmer_count()                                 kmer_dht->get_avg_kmer_count()
+//
+// Declarations mirrored: src/kcount/kcount.hpp:56-72, src/kcount/kmer_dht.hpp:57-182, src/packed_reads.hpp:72-201,
+// src/kmer.hpp:58-110. UPC++ is absent, so dist_object<T> is a local holder (operator-> / operator*), the supermer
+// RPC store is replaced by the device-side bins + kc_exchange_* (multi-rank callers plug their transport into
+// KmerDHT::exchange_hook), and errors are C++ exceptions (kc_error) instead of DIE().
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <functional>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "kcount_b200.h"
+
+namespace kcount_b200 {
+
+struct kc_error : std::runtime_error {
+  int code;
+  kc_error(int c, const std::string &msg) : std::runtime_error("kcount_b200 error " + std::to_string(c) + ": " + msg), code(c) {}
+};
+
+using kmer_count_t = uint16_t;  // src/kcount/kmer_dht.hpp:55
+inline int _dmin_thres = 2;     // process-wide in the reference as well (src/kcount/kmer_dht.hpp:57)
+
+template <typename T>
+class dist_object {  // stand-in for upcxx::dist_object: one instance per process
+  std::unique_ptr<T> obj;
+
+ public:
+  template <typename... A>
+  explicit dist_object(A &&...a) : obj(new T(std::forward<A>(a)...)) {}
+  T *operator->() { return obj.get(); }
+  T &operator*() { return *obj; }
+  const T *operator->() const { return obj.get(); }
+};
+
+// ---- Kmer<MAX_K> (src/kmer.hpp:58-110): N_LONGS words, base i at bits 2*(31 - i%32) of word i/32, A0 C1 G2 T3
+template <int MAX_K>
+struct Kmer {
+  static constexpr int N_LONGS = (MAX_K + 31) / 32;
+  inline static unsigned int k = 0;
+  uint64_t longs[N_LONGS] = {};
+
+  static void set_k(unsigned int kk) { k = kk; }
+  static unsigned int get_k() { return k; }
+  static int get_N_LONGS() { return N_LONGS; }
+  Kmer() = default;
+  explicit Kmer(const char *s) {  // Kmer::set_kmer (src/kmer.cpp:303-325): case-insensitive, N -> G
+    for (unsigned i = 0; i < k; i++) {
+      uint64_t x = ((uint64_t)s[i] & 4) >> 1;
+      x += (x ^ ((uint64_t)s[i] & 2)) >> 1;
+      longs[i / 32] |= x << (2 * (31 - i % 32));
+    }
+  }
+  explicit Kmer(const uint64_t *w) { std::memcpy(longs, w, sizeof longs); }
+  bool operator<(const Kmer &o) const {  // src/kmer.cpp:271-277
+    for (int i = 0; i < N_LONGS; i++) {
+      if (longs[i] < o.longs[i]) return true;
+      if (longs[i] > o.longs[i]) return false;
+    }
+    return false;
+  }
+  bool operator==(const Kmer &o) const { return !std::memcmp(longs, o.longs, sizeof longs); }
+  Kmer revcomp() const {  // src/kmer.cpp:491-510
+    Kmer r;
+    for (unsigned i = 0; i < k; i++) {
+      uint64_t b = (longs[i / 32] >> (2 * (31 - i % 32))) & 3;
+      unsigned j = k - 1 - i;
+      r.longs[j / 32] |= (3 - b) << (2 * (31 - j % 32));
+    }
+    return r;
+  }
+  std::string to_string() const {
+    std::string s(k, 'A');
+    for (unsigned i = 0; i < k; i++) s[i] = "ACGT"[(longs[i / 32] >> (2 * (31 - i % 32))) & 3];
+    return s;
+  }
+};
+
+struct KmerCounts {  // src/kcount/kmer_dht.hpp:62-68
+  void *uutig_frag = nullptr;
+  kmer_count_t count = 0;
+  char left = 0, right = 0;
+};
+
+struct Supermer {  // src/kcount/kmer_dht.hpp:78-90 (wire unit of the reference; here only for add_supermer callers)
+  std::string seq;
+  kmer_count_t count;
+};
+
+// ---- PackedReads (src/packed_reads.hpp:130-201): the part a kcount caller touches. Bytes are the reference's own
+// encoding (src/packed_reads.cpp:99-126): base(A0 C1 G2 T3 N4) | min(qual - offset, 31) << 3, one byte per base.
+class PackedReads {
+  int qual_offset;
+  std::string fname;
+  std::vector<uint8_t> bytes;
+  std::vector<uint64_t> offsets;
+  std::vector<uint16_t> lens;
+  uint64_t index = 0;
+
+ public:
+  PackedReads(int qual_offset, const std::string &fname = "") : qual_offset(qual_offset), fname(fname) {}
+  void add_read(const std::string & /*read_id*/, const std::string &seq, const std::string &quals) {  // packed_reads.cpp:344-352
+    offsets.push_back(bytes.size());
+    lens.push_back((uint16_t)seq.size());
+    for (size_t i = 0; i < seq.size(); i++) {
+      uint8_t b = 4;
+      switch (seq[i]) {
+        case 'A': case 'a': b = 0; break;
+        case 'C': case 'c': b = 1; break;
+        case 'G': case 'g': b = 2; break;
+        case 'T': case 't': b = 3; break;
+      }
+      int q = (int)(unsigned char)quals[i] - qual_offset;
+      bytes.push_back((uint8_t)(b | ((q > 31 ? 31 : (q < 0 ? 0 : q)) << 3)));
+    }
+  }
+  // adopt an existing PackedRead byte stream (e.g. the reference's allocator blocks flattened by the caller)
+  void add_packed(const uint8_t *b, uint64_t n_bytes, const uint64_t *off, const uint16_t *len, uint64_t n_reads) {
+    const uint64_t base = bytes.size();
+    bytes.insert(bytes.end(), b, b + n_bytes);
+    for (uint64_t i = 0; i < n_reads; i++) {
+      offsets.push_back(base + off[i]);
+      lens.push_back(len[i]);
+    }
+  }
+  uint64_t get_local_num_reads() const { return lens.size(); }
+  int get_qual_offset() const { return qual_offset; }
+  void reset() { index = 0; }
+  const std::vector<uint8_t> &raw_bytes() const { return bytes; }
+  const std::vector<uint64_t> &raw_offsets() const { return offsets; }
+  const std::vector<uint16_t> &raw_lens() const { return lens; }
+  static uint64_t get_total_local_num_reads(const std::vector<PackedReads *> &l) {
+    uint64_t n = 0;
+    for (auto *p : l) n += p->get_local_num_reads();
+    return n;
+  }
+  // src/packed_reads.cpp:484-518: k-mers of the first 50 000 reads of each file, scaled to all reads
+  static uint64_t estimate_num_kmers(unsigned kmer_len, const std::vector<PackedReads *> &l) {
+    uint64_t num_kmers = 0, num_reads = 0, tot = get_total_local_num_reads(l);
+    for (auto *p : l) {
+      for (uint64_t i = 0; i < p->lens.size() && i < 50000; i++) {
+        if (p->lens[i] < kmer_len) continue;
+        num_kmers += p->lens[i] - kmer_len + 1;
+        num_reads++;
+      }
+    }
+    return num_reads ? num_kmers * tot / num_reads : 0;
+  }
+};
+using PackedReadsList = std::vector<PackedReads *>;  // src/packed_reads.hpp:201 (a deque there)
+
+// ---- KmerDHT<MAX_K> (src/kcount/kmer_dht.hpp:118-182). One instance per rank.
+template <int MAX_K>
+class KmerDHT {
+  kc_ctx *ctx = nullptr;
+  kc_stats stats{};
+  double avg_kmer_count = 0;
+  bool finished = false;
+  int n_ranks = 1;
+
+  void ck(int rc) const {
+    if (rc != KC_OK) throw kc_error(rc, kc_last_error(ctx));
+  }
+
+ public:
+  // multi-rank callers: moves every rank's per-owner regions to their owners between kc_parse and kc_insert
+  // (kc_exchange_send_sizes / send_ptr / recv_buffer / recv_offsets, then the transport, then kc_exchange_done)
+  std::function<void(kc_ctx *)> exchange_hook;
+
+  // same parameter list as the reference constructor (kmer_dht.cpp:104-111) without the upcxx team; rank / n_ranks /
+  // device are what upcxx::rank_me(), rank_n() and init_devices() supply there
+  KmerDHT(uint64_t my_num_kmers, size_t /*my_num_ctg_kmers*/, size_t /*max_kmer_store_bytes*/, int /*max_rpcs_in_flight*/, bool use_qf,
+          int sequencing_depth, int rank = 0, int n_ranks = 1, int device = -1, uint32_t flags = 0)
+      : n_ranks(n_ranks) {
+    if (!my_num_kmers) throw kc_error(KC_ERR_ARG, "no kmers to reserve space for");
+    kc_config cfg;
+    kc_config_default(&cfg);
+    cfg.k = Kmer<MAX_K>::get_k();
+    cfg.dmin_thres = _dmin_thres;
+    cfg.use_filter = use_qf;
+    cfg.rank = rank;
+    cfg.n_ranks = n_ranks;
+    cfg.device = device;
+    cfg.est_kmers = my_num_kmers;
+    cfg.sequencing_depth = sequencing_depth;
+    cfg.flags = flags;
+    int rc = kc_create(&cfg, &ctx);
+    if (rc != KC_OK) throw kc_error(rc, kc_last_error(nullptr));
+  }
+  ~KmerDHT() { kc_destroy(ctx); }
+  KmerDHT(const KmerDHT &) = delete;
+  KmerDHT &operator=(const KmerDHT &) = delete;
+
+  kc_ctx *context() { return ctx; }
+  void clear_stores() {}
+  int get_minimizer_len() const { return (int)kc_minimizer_len(ctx); }
+  uint64_t get_local_num_kmers() {
+    uint64_t n = 0;
+    if (finished) ck(kc_result_size(ctx, 0, &n));
+    return n;
+  }
+  uint64_t get_num_kmers(bool /*all*/ = false) { return get_local_num_kmers(); }  // single rank; reduce over ranks in the caller
+  int get_kmer_target_rank(const Kmer<MAX_K> &kmer, const Kmer<MAX_K> *kmer_rc = nullptr) const {  // kmer_dht.cpp:193-196
+    Kmer<MAX_K> rc = kmer_rc ? *kmer_rc : kmer.revcomp();
+    return kc_owner_of(ctx, (rc < kmer ? rc : kmer).longs);
+  }
+  KmerCounts *get_local_kmer_counts(const Kmer<MAX_K> &kmer) {  // kmer_dht.cpp:199-207; pointer valid until the next call
+    static thread_local KmerCounts kc;
+    uint16_t c = 0;
+    char l = 0, r = 0;
+    ck(kc_lookup(ctx, kmer.longs, 1, &c, &l, &r));
+    if (!c) return nullptr;
+    kc.count = c;
+    kc.left = l;
+    kc.right = r;
+    return &kc;
+  }
+  bool kmer_exists(const Kmer<MAX_K> &kmer_fw) {  // kmer_dht.cpp:225-233
+    Kmer<MAX_K> rc = kmer_fw.revcomp();
+    return get_local_kmer_counts(rc < kmer_fw ? rc : kmer_fw) != nullptr;
+  }
+  kmer_count_t get_kmer_count(const Kmer<MAX_K> &kmer_fw) {  // kmer_dht.cpp:235-245
+    Kmer<MAX_K> rc = kmer_fw.revcomp();
+    KmerCounts *kc = get_local_kmer_counts(rc < kmer_fw ? rc : kmer_fw);
+    return kc ? kc->count : 0;
+  }
+  uint64_t get_num_supermer_inserts() const { return stats.supermers_in; }
+  double get_avg_kmer_count() const { return avg_kmer_count; }
+  void set_avg_kmer_count(double v) { avg_kmer_count = v; }
+  const kc_stats &get_stats() const { return stats; }
+
+  // count_kmers' hand-over of the local reads (kcount.cpp:71-90); the supermer cut happens on the device
+  void add_reads(const PackedReads &pr) {
+    if (pr.get_local_num_reads())
+      ck(kc_add_reads(ctx, pr.raw_bytes().data(), pr.raw_bytes().size(), pr.raw_offsets().data(), pr.raw_lens().data(),
+                      pr.get_local_num_reads()));
+  }
+  void flush_updates() {  // kmer_dht.cpp:253-258
+    ck(kc_parse(ctx));
+    if (n_ranks > 1) {
+      if (!exchange_hook) throw kc_error(KC_ERR_STATE, "multi-rank KmerDHT needs an exchange_hook");
+      exchange_hook(ctx);
+    }
+    ck(kc_insert(ctx));
+  }
+  void finish_updates() {  // kmer_dht.cpp:261-267 -> insert_into_local_hashtable
+    ck(kc_finalize(ctx, &stats));
+    avg_kmer_count = stats.avg_kmer_count;
+    finished = true;
+  }
+  void dump_kmers(const std::string &path = "") {  // kmer_dht.cpp:274-297 (here: sorted, uncompressed)
+    std::string p = path.empty() ? "kmers-" + std::to_string(Kmer<MAX_K>::get_k()) + ".txt" : path;
+    ck(kc_dump_sorted(ctx, p.c_str(), 0));
+  }
+  // local_kmers_begin/end (kmer_dht.cpp:300-307): the dense result instead of a host hash map
+  struct LocalKmers {
+    std::vector<uint64_t> keys;  // [n * N_LONGS]
+    std::vector<uint16_t> counts;
+    std::vector<char> left, right;
+    size_t size() const { return counts.size(); }
+    Kmer<MAX_K> kmer(size_t i) const { return Kmer<MAX_K>(&keys[i * Kmer<MAX_K>::N_LONGS]); }
+    KmerCounts counts_of(size_t i) const { return KmerCounts{nullptr, counts[i], left[i], right[i]}; }
+  };
+  LocalKmers local_kmers(bool sorted = false) {
+    LocalKmers r;
+    uint64_t n = get_local_num_kmers();
+    if (sorted) ck(kc_result_sort(ctx, 0));
+    r.keys.resize(n * kc_key_words(ctx));
+    r.counts.resize(n);
+    r.left.resize(n);
+    r.right.resize(n);
+    if (n) ck(kc_result_copy(ctx, 0, r.keys.data(), r.counts.data(), r.left.data(), r.right.data(), nullptr));
+    return r;
+  }
+};
+
+// ---- analyze_kmers<MAX_K> (src/kcount/kcount.hpp:70-72, src/kcount/kcount.cpp:143-161)
+template <int MAX_K>
+void analyze_kmers(unsigned kmer_len, int qual_offset, PackedReadsList &packed_reads_list, int dmin_thres,
+                   dist_object<KmerDHT<MAX_K>> &kmer_dht, bool dump_kmers) {
+  if (kmer_len != Kmer<MAX_K>::get_k()) throw kc_error(KC_ERR_ARG, "analyze_kmers: kmer_len differs from Kmer<MAX_K>::k");
+  if (dmin_thres != _dmin_thres) throw kc_error(KC_ERR_ARG, "analyze_kmers: set kcount_b200::_dmin_thres before constructing the KmerDHT");
+  for (auto *pr : packed_reads_list) {
+    if (pr->get_qual_offset() != qual_offset) throw kc_error(KC_ERR_ARG, "analyze_kmers: qual_offset differs from the reads'");
+    kmer_dht->add_reads(*pr);  // count_kmers
+  }
+  kmer_dht->flush_updates();
+  kmer_dht->finish_updates();
+  if (dump_kmers) kmer_dht->dump_kmers();
+  kmer_dht->clear_stores();
+}
+
+}  // namespace kcount_b200
