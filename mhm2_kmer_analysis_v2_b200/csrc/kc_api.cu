@@ -159,8 +159,8 @@ static void configure_bins(kc_ctx *c) {
         P = 8192;  // no rank-independent estimate: a fixed count keeps the ranks' headers compatible; big bins are split
       } else {
         const double distinct = (double)est / depth + (double)est * kmer_err;
-        const double per_bin = 0.55 * count_table_slots(c->N, R_multi);
-        P = (uint32_t)std::min<double>(std::ceil(distinct / per_bin), (double)(1u << 22));
+        const double per_bin = 0.6 * count_table_slots(c->N, R_multi, c->k);
+        P = (uint32_t)std::min<double>(std::ceil(distinct / per_bin), (double)(1u << 23));
         if (P < 1) P = 1;
       }
     } else {
@@ -191,7 +191,7 @@ static void configure_bins(kc_ctx *c) {
   c->n_ids = n_ids;
   c->rec_bytes = R;
   c->header_bytes = (int)((((uint64_t)P * 8 + kHeaderAlign - 1) / kHeaderAlign) * kHeaderAlign);
-  c->count_slots = c->resident ? count_table_slots(c->N, R) : 0;
+  c->count_slots = c->resident ? count_table_slots(c->N, R, c->k) : 0;
 }
 
 // ------------------------------------------------------------------------------------------------ lifecycle
@@ -235,7 +235,7 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   if (m < 1 || m > 28) return fail(c, KC_ERR_ARG, "kc_create: minimizer length %d unsupported (1..28)", m);
   const bool resident = !cfg->use_filter && !(cfg->flags & KC_FLAG_GLOBAL_TABLE);
   if (!resident && (cfg->local_bins & (cfg->local_bins - 1))) return fail(c, KC_ERR_ARG, "kc_create: local_bins must be a power of two in HBM-table mode");
-  if (cfg->local_bins > (1u << 22) || (uint64_t)std::max(cfg->local_bins, 1u) * cfg->n_ranks > (1u << 25))
+  if (cfg->local_bins > (1u << 23) || (uint64_t)std::max(cfg->local_bins, 1u) * cfg->n_ranks > (1u << 25))
     return fail(c, KC_ERR_ARG, "kc_create: too many bins");
   if (cfg->record_bytes && cfg->record_bytes != 16 && cfg->record_bytes != 32 && cfg->record_bytes != 64)
     return fail(c, KC_ERR_ARG, "kc_create: record_bytes must be 16, 32 or 64");
@@ -716,7 +716,7 @@ static int launch_count_pass(kc_ctx *c) {
   cp.header_bytes = c->header_bytes;
   cp.src_ptr = c->d_count_src;
   cp.n_slots = c->count_slots;
-  cp.claim_limit = (uint32_t)(0.9 * c->count_slots);
+  cp.claim_limit = (uint32_t)(0.85 * c->count_slots);
   cp.dmin_thres = c->cfg.dmin_thres;
   cp.keep_ext = keep_ext;
   cp.one_minus_dyn = 1.0 - c->cfg.dyn_min_depth;  // evaluated on the host exactly as the reference's constant expression

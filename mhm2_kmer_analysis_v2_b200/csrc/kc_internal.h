@@ -164,16 +164,17 @@ cudaError_t launch_checksum(const uint64_t *keys, const uint16_t *counts, const 
 
 // ---- bin-resident counting (kc_count.cu) ----------------------------------------
 // The default path: every local bin is small enough that the distinct k-mers of the bin fit a hash table in shared
-// memory; one CTA counts a bin there and emits the purged / extension-resolved entries straight to the dense result.
+// memory; one WARP counts a bin there and emits the purged / extension-resolved entries straight to the dense result.
 static const int kCountMaxSrc = 64;    // source ranks per owner the count kernel can read from
-static const int kCountMaxHeavy = 64;  // keys with more than 65535 occurrences per (bin, split pass)
+static const int kCountMaxHeavy = 8;   // keys with more than 65535 occurrences per (bin, split pass)
 
 struct CountParams {
   int k, rec_bytes, n_src, tile_records;
   uint32_t n_bins;
   int header_bytes;                  // bytes of the per-source header block [n_bins x {u32 first_record, u32 n_records}]
   const uint8_t *const *src_ptr;     // [n_src] region of each source rank for this owner (nullptr = nothing received)
-  uint32_t n_slots;                  // table slots in shared memory
+  uint32_t n_slots;                  // table slots in shared memory (per warp)
+  int warp_bytes;                    // shared memory of one warp (set by launch_count)
   uint32_t claim_limit;              // claimed slots at which a pass gives up and the bin is split further
   int dmin_thres, keep_ext;
   double one_minus_dyn;
@@ -188,7 +189,7 @@ struct CountParams {
   uint64_t cap_ext;
 };
 // slots that fit the shared-memory budget of one CTA for N key words
-uint32_t count_table_slots(int n_words, int rec_bytes);
+uint32_t count_table_slots(int n_words, int rec_bytes, int k);
 cudaError_t launch_count(const CountParams &p, int n_words, bool merge_runs, int sm_count, cudaStream_t s, uint64_t *launches);
 
 static const int kHeaderAlign = 64;
