@@ -212,6 +212,7 @@ def main():
     ap.add_argument("--cpu-sample-reads", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--n-genomes", type=int, default=0, help="profiling only: fewer genomes keep the coverage of a smaller read set like the full workload's")
     ap.add_argument("--phase-detail", action="store_true", help="also print per-phase device times to stderr")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
@@ -246,7 +247,10 @@ def main():
     k, n = args.k, args.reads_per_gpu
     # ---- this rank's reads, generated straight into pinned host memory
     pin_reads = PinnedBuffer(n * READ_LEN)
-    syn = K.Synth(**K.CONFIGS[WORKLOAD]["synth"])
+    synth_kw = dict(K.CONFIGS[WORKLOAD]["synth"])
+    if args.n_genomes:
+        synth_kw["n_genomes"] = args.n_genomes
+    syn = K.Synth(**synth_kw)
     t0 = time.perf_counter()
     reads = syn.generate(rank * n, n, out_bytes=pin_reads.array)
     syn.close()

@@ -41,6 +41,13 @@ struct kc_ctx {
   bool resident = true;       // bin-resident shared-memory counting (kc_count.cu) vs one table in HBM (kc_insert.cu)
   uint32_t count_slots = 0;   // resident: table slots per CTA
   uint8_t **d_count_src = nullptr;
+  // two-level partition: P coarse bins per owner (parse, layout, exchange), each refined into 1 << fine_shift fine bins
+  // (kc_refine.cu) before counting
+  uint32_t fine_shift = 0;
+  uint8_t *d_fine = nullptr;
+  uint64_t fine_alloc = 0;
+  unsigned long long *d_coarse_base = nullptr;
+  uint64_t coarse_base_alloc = 0;
   int device = 0, sm_count = 148;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -160,7 +167,7 @@ static void configure_bins(kc_ctx *c) {
       } else {
         const double distinct = (double)est / depth + (double)est * kmer_err;
         const double per_bin = 0.6 * count_table_slots(c->N, R_multi, c->k);
-        P = (uint32_t)std::min<double>(std::ceil(distinct / per_bin), (double)(1u << 23));
+        P = (uint32_t)std::min<double>(std::ceil(distinct / per_bin), (double)(1u << 26));
         if (P < 1) P = 1;
       }
     } else {
@@ -170,7 +177,15 @@ static void configure_bins(kc_ctx *c) {
       P = table_bytes > 512e6 ? 1024 : 1;
     }
   }
+  // P so far is the number of FINE bins the count kernel wants. Beyond 64 K of them the parse routes by coarse bin
+  // (16 fine bins each) and kc_refine.cu does the second level.
+  uint32_t fine_shift = 0;
+  if (c->resident && P >= 65536u) {
+    fine_shift = 4;
+    P = (P + 15u) >> 4;
+  }
   while ((uint64_t)P * c->G > (1u << 25)) P /= 2;
+  c->fine_shift = fine_shift;
   const uint32_t n_ids = P * (uint32_t)c->G;
   int R = cfg.record_bytes ? (int)cfg.record_bytes : auto_record_bytes(c->k, c->m, (int)n_ids);
   while (record_geom(R, c->k).max_kmers < 1 && R < 64) R *= 2;
@@ -235,7 +250,7 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   if (m < 1 || m > 28) return fail(c, KC_ERR_ARG, "kc_create: minimizer length %d unsupported (1..28)", m);
   const bool resident = !cfg->use_filter && !(cfg->flags & KC_FLAG_GLOBAL_TABLE);
   if (!resident && (cfg->local_bins & (cfg->local_bins - 1))) return fail(c, KC_ERR_ARG, "kc_create: local_bins must be a power of two in HBM-table mode");
-  if (cfg->local_bins > (1u << 23) || (uint64_t)std::max(cfg->local_bins, 1u) * cfg->n_ranks > (1u << 25))
+  if (cfg->local_bins > (1u << 26) || (!resident && (uint64_t)std::max(cfg->local_bins, 1u) * cfg->n_ranks > (1u << 25)))
     return fail(c, KC_ERR_ARG, "kc_create: too many bins");
   if (cfg->record_bytes && cfg->record_bytes != 16 && cfg->record_bytes != 32 && cfg->record_bytes != 64)
     return fail(c, KC_ERR_ARG, "kc_create: record_bytes must be 16, 32 or 64");
@@ -324,6 +339,8 @@ extern "C" void kc_destroy(kc_ctx *c) {
   dev_free(c->d_recv);
   dev_free(c->d_src_ptr);
   dev_free(c->d_count_src);
+  dev_free(c->d_fine);
+  dev_free(c->d_coarse_base);
   dev_free(c->d_segments);
   dev_free(c->d_seg_tile_start);
   dev_free(c->d_regions);
@@ -401,6 +418,7 @@ static ParseParams parse_params(kc_ctx *c, const ReadChunk &ch, uint32_t stride,
   p.rec_bytes = c->rec_bytes;
   p.n_ids = c->n_ids;
   p.local_bins = (uint32_t)c->P;
+  p.fine_shift = c->fine_shift;
   p.div_ranks = make_fastdiv(c->G);
   p.bins = c->d_bins;
   p.bin_base = c->d_bin_base;
@@ -424,6 +442,7 @@ static int layout_bins(kc_ctx *c, uint32_t stride) {
   lp.header_bytes = c->header_bytes;
   lp.pad = 64;
   lp.bin_cursor = c->d_cursor;
+  lp.sampled_total = &c->d_ctr->parse_records;
   lp.bin_cap = c->d_bin_cap;
   lp.bin_first = c->d_bin_first;
   lp.bin_base = c->d_bin_base;
@@ -481,15 +500,16 @@ static int estimate_caps(kc_ctx *c) {
   const uint32_t n = c->n_ids;
   int rc = ensure_bin_arrays(c);
   if (rc) return rc;
-  // sample: at least 262144 reads, and about 24 records per bin (a read yields ~2 (L-k-1) / (k-m+2) + 1 of them)
+  // sample: at least 262144 reads, and about 64 records per bin (a read yields ~2 (L-k-1) / (k-m+2) + 1 of them)
   uint64_t want_reads = 262144;
   if (n > 1) {
     const double avg_len = c->n_reads ? (double)c->n_bases / (double)c->n_reads : 0.0;
     const double per_read = std::max(1.0, 2.0 * std::max(avg_len - c->k - 1, 0.0) / (double)(c->k - c->m + 2) + 1.0);
-    want_reads = std::max<uint64_t>(want_reads, (uint64_t)(24.0 * n / per_read));
+    want_reads = std::max<uint64_t>(want_reads, (uint64_t)(64.0 * n / per_read));
   }
   uint32_t stride = (uint32_t)std::max<uint64_t>(1, c->n_reads / want_reads);
   CK(cudaMemsetAsync(c->d_cursor, 0, n * sizeof(unsigned long long), c->stream));
+  CK(cudaMemsetAsync(&c->d_ctr->parse_counted, 0, 3 * sizeof(unsigned long long) + sizeof(unsigned int), c->stream));
   for (auto &ch : c->chunks) {
     ParseParams p = parse_params(c, ch, stride, 1);
     CK(launch_parse(p, c->sm_count, c->stream, &c->launches));
@@ -534,6 +554,20 @@ extern "C" int kc_parse(kc_ctx *c) {
   CK(cudaStreamSynchronize(c->stream));
   if (c->h_ctr.err_bins_full) {
     // the sample under-estimated a bin: the cursors now hold the exact demand, lay out again and redo
+    if (getenv("KC_DEBUG")) {
+      std::vector<unsigned long long> cur(c->n_ids);
+      std::vector<uint64_t> cap(c->n_ids);
+      cudaMemcpy(cur.data(), c->d_cursor, c->n_ids * 8, cudaMemcpyDeviceToHost);
+      cudaMemcpy(cap.data(), c->d_bin_cap, c->n_ids * 8, cudaMemcpyDeviceToHost);
+      uint64_t n_over = 0, sum = 0, sumcap = 0;
+      for (uint32_t i = 0; i < c->n_ids; i++) {
+        sum += cur[i];
+        sumcap += cap[i];
+        if (cur[i] > cap[i] && n_over++ < 8) fprintf(stderr, "[kc] bin %u: %llu records, capacity %llu\n", i, cur[i], (unsigned long long)cap[i]);
+      }
+      fprintf(stderr, "[kc] %llu of %u bins overflowed; %llu records, capacity %llu\n", (unsigned long long)n_over, c->n_ids,
+              (unsigned long long)sum, (unsigned long long)sumcap);
+    }
     rc = layout_bins(c, 1);
     if (rc) return rc;
     rc = run_parse(c);
@@ -703,6 +737,48 @@ static InsertParams insert_params(kc_ctx *c) {
 
 static int alloc_results(kc_ctx *c, ResultSet &r, uint64_t cap, bool with_ext);
 
+static int fine_header_bytes(const kc_ctx *c) {
+  return (int)(((((uint64_t)c->P << c->fine_shift) * 8) + kHeaderAlign - 1) / kHeaderAlign * kHeaderAlign);
+}
+
+// second partition level: the coarse bins of every source -> one region of fine bins (d_fine), the count kernel's only source
+static int refine_bins(kc_ctx *c) {
+  RefineParams rp;
+  memset(&rp, 0, sizeof rp);
+  rp.n_src = c->G;
+  rp.rec_bytes = c->rec_bytes;
+  rp.n_coarse = (uint32_t)c->P;
+  rp.fine_shift = c->fine_shift;
+  rp.src_header_bytes = c->header_bytes;
+  rp.src_ptr = c->d_count_src;
+  rp.dst_header_bytes = fine_header_bytes(c);
+  if (c->coarse_base_alloc < (uint64_t)c->P + 2) {
+    dev_free(c->d_coarse_base);
+    CK(dev_alloc(&c->d_coarse_base, (uint64_t)c->P + 2));
+    c->coarse_base_alloc = (uint64_t)c->P + 2;
+  }
+  rp.coarse_base = c->d_coarse_base;
+  rp.total = c->d_coarse_base + c->P + 1;
+  rp.err_too_large = &c->d_ctr->err_bins_full;
+  CK(launch_refine_totals(rp, c->stream, &c->launches));
+  unsigned long long total = 0;
+  CK(cudaMemcpyAsync(&total, rp.total, sizeof total, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (total > 0xffffffffULL) return fail(c, KC_ERR_ARG, "more than 2^32 supermer records for one rank; use more ranks");
+  const uint64_t need = (uint64_t)rp.dst_header_bytes + total * c->rec_bytes + 256;
+  if (need > c->fine_alloc) {
+    dev_free(c->d_fine);
+    CK(dev_alloc(&c->d_fine, need + need / 16));
+    c->fine_alloc = need + need / 16;
+  }
+  rp.dst = c->d_fine;
+  CK(launch_refine(rp, c->sm_count, c->stream, &c->launches));
+  uint8_t *fine = c->d_fine;
+  CK(cudaMemcpyAsync(c->d_count_src + kCountMaxSrc, &fine, sizeof fine, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));  // `fine` is a local
+  return KC_OK;
+}
+
 // ---- bin-resident counting: one fused kernel does insert + purge + extension resolution + compaction
 static int launch_count_pass(kc_ctx *c) {
   const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
@@ -710,11 +786,11 @@ static int launch_count_pass(kc_ctx *c) {
   memset(&cp, 0, sizeof cp);
   cp.k = c->k;
   cp.rec_bytes = c->rec_bytes;
-  cp.n_src = c->G;
+  cp.n_src = c->fine_shift ? 1 : c->G;
   cp.tile_records = insert_tile_records(c->rec_bytes);
-  cp.n_bins = (uint32_t)c->P;
-  cp.header_bytes = c->header_bytes;
-  cp.src_ptr = c->d_count_src;
+  cp.n_bins = (uint32_t)c->P << c->fine_shift;
+  cp.header_bytes = c->fine_shift ? fine_header_bytes(c) : c->header_bytes;
+  cp.src_ptr = c->fine_shift ? c->d_count_src + kCountMaxSrc : c->d_count_src;
   cp.n_slots = c->count_slots;
   cp.claim_limit = (uint32_t)(0.85 * c->count_slots);
   cp.dmin_thres = c->cfg.dmin_thres;
@@ -742,7 +818,7 @@ static int launch_count_pass(kc_ctx *c) {
 
 static int insert_resident(kc_ctx *c, const std::vector<uint8_t *> &src) {
   const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
-  if (!c->d_count_src) CK(dev_alloc(&c->d_count_src, kCountMaxSrc));
+  if (!c->d_count_src) CK(dev_alloc(&c->d_count_src, 2 * kCountMaxSrc));
   CK(cudaMemcpyAsync(c->d_count_src, src.data(), c->G * sizeof(uint8_t *), cudaMemcpyHostToDevice, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   // result capacity: an entry that is written has count >= 2, so occurrences / 2 bounds it; the occurrences this owner
@@ -767,6 +843,10 @@ static int insert_resident(kc_ctx *c, const std::vector<uint8_t *> &src) {
   }
   CK(cudaEventRecord(c->ev0, c->stream));
   c->stats.insert_kernel_launches = 1;
+  if (c->fine_shift) {
+    int rrc = refine_bins(c);
+    if (rrc) return rrc;
+  }
   int rc = launch_count_pass(c);
   if (rc) return rc;
   CK(cudaEventRecord(c->ev1, c->stream));
@@ -919,7 +999,7 @@ static void fill_stats(kc_ctx *c) {
   s.table_slots = c->resident ? c->count_slots : c->table_slots;
   s.table_bytes = c->resident ? 0 : c->table_slots * slot_bytes(c->N);
   s.filter_bytes = c->resident ? 0 : c->filter_buckets * 32;
-  s.local_bins = (uint64_t)c->P;
+  s.local_bins = (uint64_t)c->P << c->fine_shift;
   s.split_passes = h.split_passes;
   s.result_bytes = c->res_final.cap * ((uint64_t)c->N * 8 + 4) + (c->res_ext.ext8 ? c->res_ext.cap * ((uint64_t)c->N * 8 + 20) : 0);
   s.avg_kmer_count = h.n_final ? (double)h.sum_counts / (double)h.n_final : 0.0;

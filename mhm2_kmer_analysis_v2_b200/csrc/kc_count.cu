@@ -260,7 +260,7 @@ __device__ __forceinline__ uint32_t stage_chunk(const CountParams &p, WarpCtx &w
 #pragma unroll
       for (int u = 0; u < U; u++) v[u] = ld_stream16(src + 16 * u);
     }
-    const uint32_t cnt = v[U - 1].w & 0xffffu;
+    const uint32_t cnt = v[U - 1].w & 0xffu;
     const uint32_t m_nz = __ballot_sync(0xffffffffu, cnt != 0u);
     uint32_t incl = cnt;
 #pragma unroll

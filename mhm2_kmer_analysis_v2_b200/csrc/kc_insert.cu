@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(THREADS, 4) insert_kernel(InsertParams p) {
     uint32_t mine = 0;
     for (int u = 0; u < rpl; u++) {
       int rr = lane * rpl + u;
-      uint32_t n = rr < nrec ? (s_rec[rr * W + W - 1] & 0xffffu) : 0u;
+      uint32_t n = rr < nrec ? (s_rec[rr * W + W - 1] & 0xffu) : 0u;
       if (n) n_records++;
       mine += n;
     }
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(THREADS, 4) insert_kernel(InsertParams p) {
       for (int u = 0; u < rpl; u++) {
         int rr = lane * rpl + u;
         s_pre[rr] = at;
-        at += rr < nrec ? (s_rec[rr * W + W - 1] & 0xffffu) : 0u;
+        at += rr < nrec ? (s_rec[rr * W + W - 1] & 0xffu) : 0u;
       }
       if (lane == 31) s_pre[T] = total;
     }
@@ -329,7 +329,7 @@ __global__ void __launch_bounds__(THREADS, 4) insert_kernel(InsertParams p) {
       rec_i = lo;
       j = q - s_pre[lo];
       rec = s_rec + rec_i * W;
-      n = rec[W - 1] & 0xffffu;
+      n = rec[W - 1] & 0xffu;
     }
     Occurrence<N> pend;
     uint32_t pend_cnt = 0;
@@ -395,7 +395,7 @@ __global__ void __launch_bounds__(THREADS, 4) insert_kernel(InsertParams p) {
               do {
                 rec_i++;
                 rec += W;
-                n = rec[W - 1] & 0xffffu;
+                n = rec[W - 1] & 0xffu;
               } while (n == 0);
               j = 0;
               fresh = true;

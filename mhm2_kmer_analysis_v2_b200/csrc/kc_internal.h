@@ -110,7 +110,8 @@ struct ParseParams {
   int count_only;
   int k, m, qual_cutoff, rec_bytes;
   uint32_t n_ids;        // n_ranks * local_bins
-  uint32_t local_bins;   // bins per owner: bin = mulhi(mix(hash / n_ranks), local_bins)
+  uint32_t local_bins;   // (coarse) bins per owner: fine bin = mulhi(mix(hash / n_ranks), local_bins << fine_shift)
+  uint32_t fine_shift;   // log2 of the refine factor: fine bin = coarse bin << fine_shift | sub-bin (record header bits 8..15)
   FastDiv div_ranks;
   uint8_t *bins;                     // record storage
   const uint64_t *bin_base;          // [n_ids] first record of each bin
@@ -145,6 +146,7 @@ struct LayoutParams {
   int rec_bytes, header_bytes;
   unsigned long long pad;                 // records added to every bin
   const unsigned long long *bin_cursor;   // [n_ids] records seen by the counting pass
+  const unsigned long long *sampled_total;  // records seen by the counting pass, all bins
   uint64_t *bin_cap, *bin_first, *bin_base;  // [n_ids] out
   unsigned long long *owner_records;      // [n_ranks] out: record capacity of each owner's area
   unsigned long long *region_off;         // [n_ranks + 1] out: byte offset of each owner's region, total at the end
@@ -191,6 +193,21 @@ struct CountParams {
 // slots that fit the shared-memory budget of one CTA for N key words
 uint32_t count_table_slots(int n_words, int rec_bytes, int k);
 cudaError_t launch_count(const CountParams &p, int n_words, bool merge_runs, int sm_count, cudaStream_t s, uint64_t *launches);
+
+// ---- second partition level (kc_refine.cu): coarse bins of every source -> one region of fine bins
+struct RefineParams {
+  int n_src, rec_bytes;
+  uint32_t n_coarse, fine_shift;
+  int src_header_bytes;            // per-source header block [n_coarse x {u32 first_record, u32 n_records}]
+  const uint8_t *const *src_ptr;   // [n_src] region of each source rank for this owner (nullptr = nothing received)
+  uint8_t *dst;                    // [fine header: (n_coarse << fine_shift) x {u32 first, u32 n}][records]
+  int dst_header_bytes;
+  unsigned long long *coarse_base; // [n_coarse + 1] records per coarse bin -> exclusive prefix
+  unsigned long long *total;       // out: records of this owner
+  unsigned int *err_too_large;
+};
+cudaError_t launch_refine_totals(const RefineParams &p, cudaStream_t s, uint64_t *launches);
+cudaError_t launch_refine(const RefineParams &p, int sm_count, cudaStream_t s, uint64_t *launches);
 
 static const int kHeaderAlign = 64;
 

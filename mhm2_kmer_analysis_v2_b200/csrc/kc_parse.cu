@@ -44,7 +44,7 @@ struct WarpQueue {
 // build the record for k-mers [start, start + n) of the segment held by lane `owner` and store it at dst
 template <int R>
 __device__ __forceinline__ void write_record(const uint32_t *s_w, const uint32_t *s_q, int owner, int lead, int start, int n, int k,
-                                             uint8_t *dst) {
+                                             uint32_t sub, uint8_t *dst) {
   constexpr int W = R / 4;
   constexpr int NBW = (R == 16 ? 32 : (R == 32 ? 80 : 160)) / 16;
   constexpr int NQW = W - NBW - (R == 32 ? 0 : 1);  // R=32: third quality word shares the header word
@@ -83,10 +83,11 @@ __device__ __forceinline__ void write_record(const uint32_t *s_w, const uint32_t
       w[NBW + v] = x;
     }
   }
+  // header: k-mers in bits 0..7, sub-bin (refined by kc_refine.cu) in bits 8..15
   if (R == 32)
-    w[W - 1] = (w[W - 1] & 0xffff0000u) | (uint32_t)n;
+    w[W - 1] = (w[W - 1] & 0xffff0000u) | (uint32_t)n | (sub << 8);
   else
-    w[W - 1] = (uint32_t)n;
+    w[W - 1] = (uint32_t)n | (sub << 8);
 #pragma unroll
   for (int i = 0; i < W / 4; i++) st_stream16(dst + 16 * i, make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]));
 }
@@ -99,7 +100,7 @@ __device__ __forceinline__ void drain(const ParseParams &p, const uint32_t *s_w,
   const uint32_t nd = min(32u, q_count);
   __syncwarp();
   const bool mine = lane < nd;
-  uint32_t id = 0, meta = 0;
+  uint32_t id = 0, meta = 0, sub = 0;
   if (mine) {
     const uint32_t e = (q_head + lane) & (QCAP - 1);
     meta = Q.meta[e];
@@ -110,7 +111,11 @@ __device__ __forceinline__ void drain(const ParseParams &p, const uint32_t *s_w,
       fast_divmod(h, p.div_ranks, q, owner);
       uint32_t x = ((uint32_t)q ^ (uint32_t)(q >> 32)) * 0x9e3779b1u;  // the high bits pick the bin
       x ^= x >> 15;
-      id = owner * p.local_bins + __umulhi(x * 0x85ebca6bu, p.local_bins);
+      // fine bin of the owner = mulhi(mix, coarse bins << fine_shift); the parse routes by the coarse bin, the low bits travel
+      // in the record header and are applied by the refine pass
+      const uint32_t fine = __umulhi(x * 0x85ebca6bu, p.local_bins << p.fine_shift);
+      id = owner * p.local_bins + (fine >> p.fine_shift);
+      sub = fine & ((1u << p.fine_shift) - 1u);
     }
   }
   // one cursor update per distinct bin of the batch (full-mask collectives: all lanes take part, idle ones stand alone)
@@ -123,7 +128,7 @@ __device__ __forceinline__ void drain(const ParseParams &p, const uint32_t *s_w,
     if (!p.count_only) {
       const unsigned long long slot = slot0 + __popc(peers & ((1u << lane) - 1u));
       if (slot < p.bin_cap[id])
-        write_record<R>(s_w, s_q, meta & 31u, (meta >> 5) & 15u, (meta >> 9) & 255u, (meta >> 17) & 255u, p.k,
+        write_record<R>(s_w, s_q, meta & 31u, (meta >> 5) & 15u, (meta >> 9) & 255u, (meta >> 17) & 255u, p.k, sub,
                         p.bins + p.bin_base[id] + slot * R);
       else
         p.ctr->err_bins_full = 1u;
@@ -403,7 +408,13 @@ __global__ void __launch_bounds__(1024) layout_caps_kernel(LayoutParams p) {
   if (b < P) {
     const double cnt = (double)p.bin_cursor[o * P + b];
     double est = cnt * p.stride;
-    if (p.stride > 1) est += 7.0 * p.stride * sqrt(cnt + 1.0) + 0.03 * est;  // sampling noise of a strided sample
+    if (p.stride > 1) {
+      est += 7.0 * p.stride * sqrt(cnt + 1.0) + 0.03 * est;  // sampling noise of a strided sample
+      // bins are filled by a hash, so a bin whose sample came out far BELOW the average is most likely just unlucky:
+      // never go under 1.25 x the average bin (a 7-sigma margin on 3 sampled records is no protection at all)
+      const double avg = (double)*p.sampled_total * p.stride / ((double)P * p.n_ranks);
+      if (est < 1.25 * avg) est = 1.25 * avg;
+    }
     cap = (unsigned long long)est + p.pad;
     p.bin_cap[o * P + b] = cap;
   }

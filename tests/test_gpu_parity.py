@@ -45,13 +45,28 @@ def test_owner_partition_matches_oracle(oracle_mod, k, G):
         st.close()
 
 
-@pytest.mark.parametrize("k,bins,rec", [(21, 16, 16), (21, 64, 0), (33, 256, 32), (55, 8, 64), (21, 1, 16), (33, 1, 32)])
+@pytest.mark.parametrize("k,bins,rec", [(21, 16, 16), (21, 64, 0), (33, 256, 32), (55, 8, 64), (21, 1, 16), (33, 1, 32),
+                                        (33, 100_000, 32), (21, 65_536, 16), (77, 200_000, 64)])
 def test_local_bins_and_record_sizes(oracle_mod, k, bins, rec):
     reads = K.generate(None, 8_000, seed=300 + k, **SMALL)
     o = oracle_run(oracle_mod, reads, k)
     st, stats = gpu_single(reads, k, local_bins=bins, record_bytes=rec)
     assert_same(st.result(True), o.result(True), f"k={k} bins={bins} rec={rec}")
     st.close()
+
+
+@pytest.mark.parametrize("k,G", [(33, 3), (55, 2)])
+def test_two_level_partition_with_owners(oracle_mod, k, G):
+    """>= 65536 fine bins: the parse routes by coarse bin, kc_refine.cu merges the G sources and sorts by fine bin."""
+    reads = K.generate(None, 8_000, seed=500 + k, **SMALL)
+    o = oracle_run(oracle_mod, reads, k, n_ranks=G)
+    stages, stats = gpu_multi(reads, k, G, local_bins=80_000)
+    for r, st in enumerate(stages):
+        assert stats[r]["local_bins"] == 80_000
+        assert_same(st.result(True), o.result(True, rank=r), f"k={k} G={G} rank {r} D2")
+    assert sum(s["inserted_kmers"] for s in stats) == reads.counted_kmers(k)
+    for st in stages:
+        st.close()
 
 
 @pytest.mark.parametrize("k", [21, 33, 77])
