@@ -35,7 +35,7 @@ namespace kc {
 
 static const int CW_WARPS = 4;        // warps per CTA (independent of each other)
 static const int CW_THREADS = CW_WARPS * 32;
-static const int CW_CTAS_PER_SM = 3;  // 12 warps per SM: the kernel is issue-bound, the table size matters more than occupancy
+static const int CW_CTAS_PER_SM = 4;  // 12 warps per SM: the kernel is issue-bound, the table size matters more than occupancy
 static const int CW_STACK = 16;       // pending (split, residue) parts of a bin
 static const int CW_TMAX = 4096;      // k-mer occurrences per staged chunk (bits of the record-start bitmap)
 static const uint32_t C_PENDING = 0xfffffffcu;
@@ -193,7 +193,7 @@ __device__ __forceinline__ uint32_t probe_warp(const Table<N> &tb, const uint64_
         } else {
           b++;
           if (b == nb) b = 0;
-          if (++probes >= nb) {  // table completely full
+          if (++probes >= min(nb, 8u)) {  // a chain of full buckets: the table is (as good as) full
             full = true;
             slot = C_NOT_FOUND;
           }
@@ -341,21 +341,22 @@ __device__ __forceinline__ void walk_chunk(const CountParams &p, const Table<N> 
     const bool sw = key_less<N>(rc, fw);  // kcount_cpu.cpp:328-333: swap and complement the extensions
 #pragma unroll
     for (int i = 0; i < N; i++) key[i] = sw ? rc[i] : fw[i];
-    const int lf = lq ? (int)lb : -1, rf = rq ? (int)rb : -1;
-    const int lr = rq ? (int)(3u - rb) : -1, rr = lq ? (int)(3u - lb) : -1;
-    const int el = sw ? lr : lf, er = sw ? rr : rf;
+    // extension letters with their "counts" flag in bit 2; reverse strand: swapped and complemented
+    const uint32_t la = lb | (lq << 2), ra = rb | (rq << 2);
+    const uint32_t el = sw ? (ra ^ 3u) : la, er = sw ? (la ^ 3u) : ra;
     const uint64_t h = count_hash<N>(key);
     const bool mine = active && (((uint32_t)(h >> 48) & wc.split_mask) == wc.split_res);  // else: another part of a split bin
     bool is_new, full = false;
     if (!HEAVY) {
       const uint32_t slot = probe_warp<N, true>(tb, key, h, mine, is_new, full);
       if (slot < C_PENDING) {
+        uint32_t *e = tb.ext + slot;
         atomicAdd(tb.cnt + slot, 1u);
-        if (el >= 0) atomicAdd(tb.ext + (uint32_t)(el >> 1) * S + slot, 1u << (16 * (el & 1)));
-        if (er >= 0) atomicAdd(tb.ext + (uint32_t)(2 + (er >> 1)) * S + slot, 1u << (16 * (er & 1)));
+        if (el & 4u) atomicAdd(e + ((el & 2u) ? S : 0u), 1u << ((el & 1u) << 4));
+        if (er & 4u) atomicAdd(e + ((er & 2u) ? 3u * S : 2u * S), 1u << ((er & 1u) << 4));
       }
-      claimed += (uint32_t)__popc(__ballot_sync(0xffffffffu, is_new));
-      if (claimed >= p.claim_limit || __any_sync(0xffffffffu, full)) {  // the pass is abandoned: the bin is split
+      claimed += is_new;  // (per lane; summed over the warp at the end of the chunk)
+      if (__any_sync(0xffffffffu, full)) {  // no room: the pass is abandoned and the bin is split
         overflow = true;
         break;
       }
@@ -365,8 +366,8 @@ __device__ __forceinline__ void walk_chunk(const CountParams &p, const Table<N> 
         const uint32_t c = tb.cnt[slot];
         if (c & kHeavyMark) {
           uint32_t *e = wc.s_heavy_side + (c & ~kHeavyMark) * 8;
-          if (el >= 0) atomicAdd(e + el, 1u);
-          if (er >= 0) atomicAdd(e + 4 + er, 1u);
+          if (el & 4u) atomicAdd(e + (el & 3u), 1u);
+          if (er & 4u) atomicAdd(e + 4 + (er & 3u), 1u);
         }
       }
     }
@@ -386,6 +387,8 @@ __device__ __forceinline__ bool walk_bin(const CountParams &p, const Table<N> &t
     n_records += n_nz;
     n_occ += occ;
     if (occ) walk_chunk<N, R, HEAVY>(p, tb, wc, occ, n_nz, claimed, overflow);
+    // too full to go on efficiently (every lane counts its own claims)
+    if (!HEAVY && !overflow && __reduce_add_sync(0xffffffffu, claimed) >= p.claim_limit) overflow = true;
   }
   return overflow;
 }
@@ -435,32 +438,61 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
 
   clear_table<N>(tb);
   const uint32_t n_warps = gridDim.x * CW_WARPS;
+  // Single source (the normal case: kc_refine.cu merged the sources): the header entries of the next two bins are kept
+  // in flight, and the records of the next bin are pulled into L2 while this one is counted, so that a warp never waits
+  // for DRAM at the top of a bin.
+  const uint2 *hdr0 = reinterpret_cast<const uint2 *>(p.src_ptr[0]);
+  const bool single = p.n_src == 1 && hdr0 != nullptr;
+  uint2 e_pre1 = make_uint2(0u, 0u), e_pre2 = make_uint2(0u, 0u);
+  {
+    const uint32_t b0 = blockIdx.x * CW_WARPS + warp;
+    if (single && b0 < p.n_bins) e_pre1 = hdr0[b0];
+    if (single && b0 + n_warps < p.n_bins) e_pre2 = hdr0[b0 + n_warps];
+  }
   for (uint32_t bin = blockIdx.x * CW_WARPS + warp; bin < p.n_bins; bin += n_warps) {
     // ---- the bin's segments: header entry {first record, n records} of every source region
     uint32_t total = 0;
+    if (single) {
+      const uint2 e = e_pre1;
+      e_pre1 = e_pre2;
+      {
+        const uint8_t *nx = p.src_ptr[0] + p.header_bytes + (uint64_t)e_pre1.x * R;
+        const uint32_t n_lines = (e_pre1.y * R + 127u) >> 7;
+        for (uint32_t l = lane; l < n_lines; l += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + (size_t)l * 128));
+      }
+      const uint64_t b2 = (uint64_t)bin + 2ull * n_warps;
+      e_pre2 = b2 < p.n_bins ? hdr0[b2] : make_uint2(0u, 0u);
+      wc.seg_ptr[0] = p.src_ptr[0] + p.header_bytes + (uint64_t)e.x * R;  // (every lane mirrors source 0)
+      wc.seg_ptr[1] = nullptr;
+      wc.seg_n[0] = e.y;
+      wc.seg_n[1] = 0;
+      wc.seg_start[0] = wc.seg_start[1] = 0;
+      total = e.y;
+    } else {
 #pragma unroll
-    for (int hs = 0; hs < 2; hs++) {
-      const int s = hs * 32 + (int)lane;
-      const uint8_t *src = (p.n_src == 1) ? p.src_ptr[0] : (s < p.n_src ? p.src_ptr[s] : nullptr);
-      uint2 e = make_uint2(0u, 0u);
-      if (src && (hs == 0 || p.n_src > 32)) e = reinterpret_cast<const uint2 *>(src)[bin];
-      if (!src || (hs == 1 && p.n_src <= 32)) e.y = 0u;
-      wc.seg_ptr[hs] = src ? src + p.header_bytes + (uint64_t)e.x * R : nullptr;
-      uint32_t cn = (p.n_src == 1 && (hs == 1)) ? 0u : e.y;
-      if (p.n_src == 1) {  // every lane mirrors source 0
-        wc.seg_n[hs] = cn;
-        wc.seg_start[hs] = 0;
-        if (hs == 0) total = cn;
-      } else {
-        uint32_t incl = cn;
+      for (int hs = 0; hs < 2; hs++) {
+        const int s = hs * 32 + (int)lane;
+        const uint8_t *src = (p.n_src == 1) ? p.src_ptr[0] : (s < p.n_src ? p.src_ptr[s] : nullptr);
+        uint2 e = make_uint2(0u, 0u);
+        if (src && (hs == 0 || p.n_src > 32)) e = reinterpret_cast<const uint2 *>(src)[bin];
+        if (!src || (hs == 1 && p.n_src <= 32)) e.y = 0u;
+        wc.seg_ptr[hs] = src ? src + p.header_bytes + (uint64_t)e.x * R : nullptr;
+        uint32_t cn = (p.n_src == 1 && (hs == 1)) ? 0u : e.y;
+        if (p.n_src == 1) {  // every lane mirrors source 0
+          wc.seg_n[hs] = cn;
+          wc.seg_start[hs] = 0;
+          if (hs == 0) total = cn;
+        } else {
+          uint32_t incl = cn;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-          if ((int)lane >= o) incl += t;
+          for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((int)lane >= o) incl += t;
+          }
+          wc.seg_n[hs] = cn;
+          wc.seg_start[hs] = total + incl - cn;
+          total += __shfl_sync(0xffffffffu, incl, 31);
         }
-        wc.seg_n[hs] = cn;
-        wc.seg_start[hs] = total + incl - cn;
-        total += __shfl_sync(0xffffffffu, incl, 31);
       }
     }
     wc.n_rec = total;
