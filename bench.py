@@ -344,25 +344,45 @@ def main():
         res_right = pin_res.view(np.uint8, final_local, offset=final_local * (N * 8 + 3))
         import ctypes as C
 
-        def e2e_pass():
+        def e2e_pass(detail=False):
+            tt = [time.perf_counter()]
+
+            def mark():
+                if detail:
+                    if detail is True:
+                        st.sync()
+                    tt.append(time.perf_counter())
+
             st.clear_reads()
+            mark()
             st.add_reads(reads)            # H2D from pinned memory, asynchronous on the stage's stream
-            s, _ = one_pass()
+            mark()
+            s, _ = one_pass()              # with the host sink set: the survivors stream out while the count kernel runs
+            mark()
             assert s["final_kmers"] == final_local, "result size changed between passes"
-            st._ck(st.L.kc_result_copy(st.h, 0, res_keys.ctypes.data, res_counts.ctypes.data, res_left.ctypes.data,
-                                       res_right.ctypes.data, None))  # D2H, synchronises
+            if detail:
+                names = ["clear_reads", "add_reads(H2D)", "parse+insert+finalize(+D2H into the sink)"]
+                print(f"e2e detail (ms, sync={detail}): " +
+                      ", ".join(f"{n} {1e3 * (b - a):.1f}" for n, a, b in zip(names, tt, tt[1:])), file=sys.stderr)
             return s
 
+        st.set_result_sink(res_keys, res_counts, res_left, res_right)
         e2e_pass()  # warm-up (allocations of the first pass)
+        if args.phase_detail:
+            e2e_pass(True)
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.e2e_steps):
-            e2e_pass()
+            e2e_pass("nosync" if os.environ.get("KC_E2E_TRACE") else False)
         barrier()
         dt = max_over_ranks(time.perf_counter() - t0)
+        # the sink really holds the result: the counts add up to the stage's own statistic
+        got = int(res_counts[:final_local].astype(np.uint64).sum())
+        assert got == int(stats["sum_counts"]), f"result sink: counts sum {got} != {stats['sum_counts']}"
+        st.set_result_sink(None)
         e2e = {"value": occ_all * args.e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": int(sum_over_ranks(float(h2d_bytes))),
                "d2h_bytes_per_step": int(sum_over_ranks(float(d2h_bytes))), "steps": args.e2e_steps, "ms_per_step": dt / args.e2e_steps * 1e3,
-               "api": "kc_add_reads(host pinned) -> kc_parse [-> NCCL all-to-all] -> kc_insert -> kc_finalize -> kc_result_copy(host pinned)"}
+               "api": "kc_set_result_sink(host pinned) + kc_add_reads(host pinned) -> kc_parse [-> NCCL all-to-all] -> kc_insert -> kc_finalize (survivors land in the sink)"}
 
     red = None
     if dist is not None:

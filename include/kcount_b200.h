@@ -179,6 +179,14 @@ int kc_result_sort(kc_ctx *ctx, int extended);
 /* Copy to HOST buffers (any may be NULL): keys[n*N] u64, counts[n] u16, left[n]/right[n] chars in
  * ACGT (or X/F when extended), ext8[n*8] u16 = lA lC lG lT rA rC rG rT (extended only). */
 int kc_result_copy(kc_ctx *ctx, int extended, uint64_t *keys, uint16_t *counts, char *left, char *right, uint16_t *ext8);
+/* Host sink for the survivors: when set before kc_insert, the entries are copied to these HOST buffers (pinned memory for
+ * full speed) WHILE the count kernel is still producing the rest, instead of by a kc_result_copy afterwards -- the
+ * device -> host hand-off HashTableInserter::done_all_inserts / insert_into_local_hashtable does at the end of the
+ * reference's GPU path (src/kcount/kcount-gpu/gpu_hash_table.cpp:737-785, src/kcount/kcount_gpu.cpp:372-506). After
+ * kc_finalize the first stats.final_kmers entries are valid (unsorted, the order of kc_result_copy without
+ * kc_result_sort). `capacity` is in entries; a result that does not fit makes kc_finalize fail with KC_ERR_ARG.
+ * keys == NULL removes the sink. */
+int kc_set_result_sink(kc_ctx *ctx, uint64_t *keys, uint16_t *counts, char *left, char *right, uint64_t capacity);
 /* Device pointers of the same arrays (valid until kc_reset/kc_destroy). */
 int kc_result_device_ptrs(kc_ctx *ctx, int extended, const uint64_t **keys, const uint16_t **counts, const char **left,
                           const char **right, const uint16_t **ext8);

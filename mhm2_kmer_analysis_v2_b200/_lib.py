@@ -82,6 +82,7 @@ PROTOTYPES = {
     "kc_result_size": (C.c_int, [vp, C.c_int, C.POINTER(C.c_uint64)]),
     "kc_result_sort": (C.c_int, [vp, C.c_int]),
     "kc_result_copy": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp]),
+    "kc_set_result_sink": (C.c_int, [vp, vp, vp, vp, vp, C.c_uint64]),
     "kc_result_device_ptrs": (C.c_int, [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "kc_result_checksum": (C.c_int, [vp, C.c_int, C.POINTER(C.c_uint64)]),
     "kc_dump_sorted": (C.c_int, [vp, C.c_char_p, C.c_int]),

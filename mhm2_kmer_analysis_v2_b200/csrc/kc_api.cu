@@ -34,6 +34,8 @@ struct ResultSet {
   bool sorted = false;
 };
 
+static const int kSinkSlices = 12;
+
 struct kc_ctx {
   kc_config cfg;
   int k = 0, m = 0, N = 0, rec_bytes = 0, P = 1, G = 1, rank = 0;
@@ -48,6 +50,16 @@ struct kc_ctx {
   uint64_t fine_alloc = 0;
   unsigned long long *d_coarse_base = nullptr;
   uint64_t coarse_base_alloc = 0;
+  // host sink for the survivors (kc_set_result_sink): the count kernel runs in slices of bins and every finished slice
+  // is copied out on a second stream while the next ones are counted
+  uint64_t *sink_keys = nullptr;
+  uint16_t *sink_counts = nullptr;
+  char *sink_left = nullptr, *sink_right = nullptr;
+  uint64_t sink_cap = 0, sink_done = 0;
+  bool sink_streamed = false;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_slice[kSinkSlices];
+  unsigned long long *h_slice_n = nullptr;  // pinned: n_final after every slice
   int device = 0, sm_count = 148;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -292,6 +304,9 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   cudaEventCreate(&c->ev_ik1);
   cudaEventCreate(&c->ev_clr);
   for (auto &e2 : c->ev_user) cudaEventCreate(&e2);
+  cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+  for (auto &e2 : c->ev_slice) cudaEventCreateWithFlags(&e2, cudaEventDisableTiming);
+  cudaHostAlloc((void **)&c->h_slice_n, kSinkSlices * sizeof(unsigned long long), cudaHostAllocDefault);
   if ((e = dev_alloc(&c->d_ctr, 1)) != cudaSuccess) return bail(e, "cudaMalloc");
   cudaMemsetAsync(c->d_ctr, 0, sizeof(DevCounters), c->stream);
   configure_bins(c);
@@ -359,6 +374,10 @@ extern "C" void kc_destroy(kc_ctx *c) {
     if (e) cudaEventDestroy(e);
   for (auto &e : c->ev_user)
     if (e) cudaEventDestroy(e);
+  for (auto &e : c->ev_slice)
+    if (e) cudaEventDestroy(e);
+  if (c->h_slice_n) cudaFreeHost(c->h_slice_n);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -367,6 +386,19 @@ extern "C" int kc_sync(kc_ctx *c) {
   if (!c) return KC_ERR_ARG;
   CK(cudaSetDevice(c->device));
   CK(cudaStreamSynchronize(c->stream));
+  CK(cudaStreamSynchronize(c->copy_stream));
+  return KC_OK;
+}
+
+extern "C" int kc_set_result_sink(kc_ctx *c, uint64_t *keys, uint16_t *counts, char *left, char *right, uint64_t capacity) {
+  if (!c) return KC_ERR_ARG;
+  if (keys && (!counts || !left || !right)) return fail(c, KC_ERR_ARG, "kc_set_result_sink: all four arrays are needed");
+  if (keys && !c->resident) return fail(c, KC_ERR_ARG, "kc_set_result_sink: needs the bin-resident count path (no filter, no global table)");
+  c->sink_keys = keys;
+  c->sink_counts = keys ? counts : nullptr;
+  c->sink_left = keys ? left : nullptr;
+  c->sink_right = keys ? right : nullptr;
+  c->sink_cap = keys ? capacity : 0;
   return KC_OK;
 }
 
@@ -780,7 +812,7 @@ static int refine_bins(kc_ctx *c) {
 }
 
 // ---- bin-resident counting: one fused kernel does insert + purge + extension resolution + compaction
-static int launch_count_pass(kc_ctx *c) {
+static int launch_count_pass(kc_ctx *c, bool stream_out = false) {
   const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
   CountParams cp;
   memset(&cp, 0, sizeof cp);
@@ -811,8 +843,41 @@ static int launch_count_pass(kc_ctx *c) {
   CK(cudaMemsetAsync(c->d_ctr, 0, offsetof(DevCounters, parse_counted), c->stream));
   CK(cudaEventRecord(c->ev_clr, c->stream));
   CK(cudaEventRecord(c->ev_ik0, c->stream));
-  CK(launch_count(cp, c->N, !(c->cfg.flags & KC_FLAG_NO_WARP_DEDUP), c->sm_count, c->stream, &c->launches));
+  const bool dedup = !(c->cfg.flags & KC_FLAG_NO_WARP_DEDUP);
+  c->sink_streamed = false;
+  c->sink_done = 0;
+  if (!stream_out || !c->sink_keys || cp.n_bins < 64u * kSinkSlices) {
+    cp.bin_begin = 0;
+    cp.bin_end = cp.n_bins;
+    CK(launch_count(cp, c->N, dedup, c->sm_count, c->stream, &c->launches));
+    CK(cudaEventRecord(c->ev_ik1, c->stream));
+    return KC_OK;
+  }
+  // Slices of bins: after every slice the result cursor comes back through pinned memory; as soon as the host sees it,
+  // the new entries [done, n) go out on the copy stream while the count stream is already busy with the next slices.
+  for (int i = 0; i < kSinkSlices; i++) {
+    cp.bin_begin = (uint32_t)((uint64_t)cp.n_bins * i / kSinkSlices);
+    cp.bin_end = (uint32_t)((uint64_t)cp.n_bins * (i + 1) / kSinkSlices);
+    CK(launch_count(cp, c->N, dedup, c->sm_count, c->stream, &c->launches));
+    CK(cudaMemcpyAsync(&c->h_slice_n[i], &c->d_ctr->n_final, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaEventRecord(c->ev_slice[i], c->stream));
+  }
   CK(cudaEventRecord(c->ev_ik1, c->stream));
+  c->sink_streamed = true;
+  const int N = c->N;
+  for (int i = 0; i < kSinkSlices; i++) {
+    CK(cudaEventSynchronize(c->ev_slice[i]));
+    uint64_t n = c->h_slice_n[i];
+    if (n > c->res_final.cap) n = c->res_final.cap;  // (the kernel flagged err_result_full: handled by kc_finalize)
+    if (n > c->sink_cap) n = c->sink_cap;
+    if (n <= c->sink_done) continue;
+    const uint64_t a = c->sink_done, m = n - a;
+    CK(cudaMemcpyAsync(c->sink_keys + a * N, c->res_final.keys + a * N, m * N * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->copy_stream));
+    CK(cudaMemcpyAsync(c->sink_counts + a, c->res_final.counts + a, m * sizeof(uint16_t), cudaMemcpyDeviceToHost, c->copy_stream));
+    CK(cudaMemcpyAsync(c->sink_left + a, c->res_final.left + a, m, cudaMemcpyDeviceToHost, c->copy_stream));
+    CK(cudaMemcpyAsync(c->sink_right + a, c->res_final.right + a, m, cudaMemcpyDeviceToHost, c->copy_stream));
+    c->sink_done = n;
+  }
   return KC_OK;
 }
 
@@ -847,7 +912,7 @@ static int insert_resident(kc_ctx *c, const std::vector<uint8_t *> &src) {
     int rrc = refine_bins(c);
     if (rrc) return rrc;
   }
-  int rc = launch_count_pass(c);
+  int rc = launch_count_pass(c, true);
   if (rc) return rc;
   CK(cudaEventRecord(c->ev1, c->stream));
   c->phase = PH_INSERTED;
@@ -875,6 +940,7 @@ static int finalize_resident(kc_ctx *c, kc_stats *stats) {
     int rc = alloc_results(c, c->res_final, c->h_ctr.n_final, false);
     if (rc) return rc;
     if (keep_ext && (rc = alloc_results(c, c->res_ext, c->h_ctr.n_ext, true))) return rc;
+    CK(cudaStreamSynchronize(c->copy_stream));
     if ((rc = launch_count_pass(c))) return rc;
     c->stats.insert_kernel_launches++;
     CK(cudaEventRecord(c->ev1, c->stream));
@@ -888,6 +954,21 @@ static int finalize_resident(kc_ctx *c, kc_stats *stats) {
     return fail(c, KC_ERR_TABLE_FULL, "bin-resident counting: a bin could not be split far enough (use more local_bins or KC_FLAG_GLOBAL_TABLE)");
   c->res_final.n = c->h_ctr.n_final;
   c->res_ext.n = keep_ext ? c->h_ctr.n_ext : 0;
+  if (c->sink_keys) {
+    if (c->res_final.n > c->sink_cap)
+      return fail(c, KC_ERR_ARG, "kc_finalize: %llu survivors do not fit the result sink (%llu entries)", (unsigned long long)c->res_final.n,
+                  (unsigned long long)c->sink_cap);
+    // whatever the slices have not sent yet (everything when the kernel was not sliced, or was repeated)
+    const uint64_t a = c->sink_streamed ? c->sink_done : 0, m = c->res_final.n - a;
+    const int N = c->N;
+    if (m) {
+      CK(cudaMemcpyAsync(c->sink_keys + a * N, c->res_final.keys + a * N, m * N * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->copy_stream));
+      CK(cudaMemcpyAsync(c->sink_counts + a, c->res_final.counts + a, m * sizeof(uint16_t), cudaMemcpyDeviceToHost, c->copy_stream));
+      CK(cudaMemcpyAsync(c->sink_left + a, c->res_final.left + a, m, cudaMemcpyDeviceToHost, c->copy_stream));
+      CK(cudaMemcpyAsync(c->sink_right + a, c->res_final.right + a, m, cudaMemcpyDeviceToHost, c->copy_stream));
+    }
+    CK(cudaStreamSynchronize(c->copy_stream));
+  }
   fill_stats(c);
   c->phase = PH_FINALIZED;
   if (stats) *stats = c->stats;

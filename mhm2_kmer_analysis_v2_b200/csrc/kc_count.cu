@@ -445,11 +445,12 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
   const bool single = p.n_src == 1 && hdr0 != nullptr;
   uint2 e_pre1 = make_uint2(0u, 0u), e_pre2 = make_uint2(0u, 0u);
   {
-    const uint32_t b0 = blockIdx.x * CW_WARPS + warp;
-    if (single && b0 < p.n_bins) e_pre1 = hdr0[b0];
-    if (single && b0 + n_warps < p.n_bins) e_pre2 = hdr0[b0 + n_warps];
+    const uint64_t b0 = (uint64_t)p.bin_begin + blockIdx.x * CW_WARPS + warp;
+    if (single && b0 < p.bin_end) e_pre1 = hdr0[b0];
+    if (single && b0 + n_warps < p.bin_end) e_pre2 = hdr0[b0 + n_warps];
   }
-  for (uint32_t bin = blockIdx.x * CW_WARPS + warp; bin < p.n_bins; bin += n_warps) {
+  for (uint64_t bin64 = (uint64_t)p.bin_begin + blockIdx.x * CW_WARPS + warp; bin64 < p.bin_end; bin64 += n_warps) {
+    const uint32_t bin = (uint32_t)bin64;
     // ---- the bin's segments: header entry {first record, n records} of every source region
     uint32_t total = 0;
     if (single) {
@@ -461,7 +462,7 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
         for (uint32_t l = lane; l < n_lines; l += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + (size_t)l * 128));
       }
       const uint64_t b2 = (uint64_t)bin + 2ull * n_warps;
-      e_pre2 = b2 < p.n_bins ? hdr0[b2] : make_uint2(0u, 0u);
+      e_pre2 = b2 < p.bin_end ? hdr0[b2] : make_uint2(0u, 0u);
       wc.seg_ptr[0] = p.src_ptr[0] + p.header_bytes + (uint64_t)e.x * R;  // (every lane mirrors source 0)
       wc.seg_ptr[1] = nullptr;
       wc.seg_n[0] = e.y;
@@ -705,7 +706,8 @@ cudaError_t launch_count(const CountParams &p_in, int n_words, bool /*merge_runs
   if (g.slots < 8 || p.n_slots != g.slots) return cudaErrorInvalidValue;
   const size_t smem = (size_t)p.warp_bytes * CW_WARPS;
   uint64_t grid = (uint64_t)sm_count * CW_CTAS_PER_SM;
-  const uint64_t need = ((uint64_t)p.n_bins + CW_WARPS - 1) / CW_WARPS;
+  if (p.bin_end == 0 && p.bin_begin == 0) p.bin_end = p.n_bins;
+  const uint64_t need = ((uint64_t)(p.bin_end - p.bin_begin) + CW_WARPS - 1) / CW_WARPS;
   if (grid > need) grid = need ? need : 1;
   (*launches)++;
   switch (n_words) {

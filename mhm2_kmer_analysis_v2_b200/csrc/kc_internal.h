@@ -173,6 +173,7 @@ static const int kCountMaxHeavy = 8;   // keys with more than 65535 occurrences 
 struct CountParams {
   int k, rec_bytes, n_src, tile_records;
   uint32_t n_bins;
+  uint32_t bin_begin, bin_end;       // bins this launch counts (a slice of [0, n_bins): results stream out slice by slice)
   int header_bytes;                  // bytes of the per-source header block [n_bins x {u32 first_record, u32 n_records}]
   const uint8_t *const *src_ptr;     // [n_src] region of each source rank for this owner (nullptr = nothing received)
   uint32_t n_slots;                  // table slots in shared memory (per warp)

@@ -106,6 +106,18 @@ class KcountStage:
     def sync(self):
         self._ck(self.L.kc_sync(self.h))
 
+    def set_result_sink(self, keys=None, counts=None, left=None, right=None):
+        """Host arrays (numpy; pinned memory for full speed) that receive the survivors while the count kernel is still
+        running -- the reference's device -> host hand-off in done_all_inserts. keys=None removes the sink. After
+        finalize() the first stats['final_kmers'] entries are valid (unsorted)."""
+        if keys is None:
+            self._ck(self.L.kc_set_result_sink(self.h, None, None, None, None, 0))
+            self._sink = None
+            return
+        cap = min(keys.size // self.N, counts.size, left.size, right.size)
+        self._sink = (keys, counts, left, right)  # keep the buffers alive
+        self._ck(self.L.kc_set_result_sink(self.h, keys.ctypes.data, counts.ctypes.data, left.ctypes.data, right.ctypes.data, cap))
+
     def stats(self):
         st = _lib.KcStats()
         self._ck(self.L.kc_get_stats(self.h, C.byref(st)))

@@ -85,3 +85,34 @@ def test_no_dedup_path(oracle_mod):
     st, _ = gpu_single(reads, 21, warp_dedup=False)
     assert_same(st.result(True), o.result(True), "no dedup")
     st.close()
+
+
+@pytest.mark.parametrize("k,bins", [(33, 100_000), (21, 0), (55, 4096)])
+def test_result_sink_streams_the_survivors(oracle_mod, k, bins):
+    """kc_set_result_sink: the survivors land in host arrays during kc_insert / kc_finalize (sliced count launches)."""
+    reads = K.generate(None, 12_000, seed=600 + k, **SMALL)
+    o = oracle_run(oracle_mod, reads, k)
+    ref = o.result(False)
+    st = K.KcountStage(k, local_bins=bins)
+    N = st.N
+    cap = len(ref) + 100
+    keys, counts = np.zeros(cap * N, np.uint64), np.zeros(cap, np.uint16)
+    left, right = np.zeros(cap, np.uint8), np.zeros(cap, np.uint8)
+    st.set_result_sink(keys, counts, left, right)
+    st.add_reads(reads)
+    stats = st.run()
+    n = stats["final_kmers"]
+    assert n == len(ref)
+    kk = keys[: n * N].reshape(n, N)
+    order = np.lexsort([kk[:, i] for i in reversed(range(N))])
+    assert np.array_equal(kk[order], ref.keys.reshape(n, N))
+    assert np.array_equal(counts[:n][order], ref.counts)
+    assert np.array_equal(left[:n][order], ref.left.view(np.uint8)) and np.array_equal(right[:n][order], ref.right.view(np.uint8))
+    # a sink that is too small is an error, not a truncation
+    st2 = K.KcountStage(k, local_bins=bins)
+    st2.set_result_sink(keys[: 10 * N], counts[:10], left[:10], right[:10])
+    st2.add_reads(reads)
+    with pytest.raises(K.KcError):
+        st2.run()
+    st.close()
+    st2.close()
