@@ -18,10 +18,13 @@ using namespace kc;
 static thread_local std::string g_create_error;
 
 struct ReadChunk {
-  uint8_t *d_bytes = nullptr;
+  uint8_t *d_bytes = nullptr;   // base of the byte buffer the offsets refer to
   uint64_t *d_offsets = nullptr;
   uint16_t *d_lens = nullptr;
   uint64_t n_reads = 0, n_bytes = 0;
+  bool owner = true;            // frees the buffers (the sub-chunks of one kc_add_reads call share them)
+  uint64_t cap_bytes = 0, cap_reads = 0;
+  cudaEvent_t ready = nullptr;  // the input copy of this chunk has arrived (recorded on in_stream)
 };
 
 enum Phase { PH_EMPTY = 0, PH_PARSED, PH_RECV_READY, PH_INSERTED, PH_FINALIZED };
@@ -58,6 +61,12 @@ struct kc_ctx {
   uint64_t sink_cap = 0, sink_done = 0;
   bool sink_streamed = false;
   cudaStream_t copy_stream = nullptr;
+  // input side: the reads of one kc_add_reads call are copied in sub-chunks on in_stream, each with its own event, so
+  // that kc_parse can start on the first reads while the rest is still crossing PCIe
+  cudaStream_t in_stream = nullptr;
+  std::vector<cudaEvent_t> ev_in_pool;
+  size_t ev_in_used = 0;
+  ReadChunk spare;  // buffers of the last kc_clear_reads, reused by the next kc_add_reads
   cudaEvent_t ev_slice[kSinkSlices];
   unsigned long long *h_slice_n = nullptr;  // pinned: n_final after every slice
   int device = 0, sm_count = 148;
@@ -305,6 +314,7 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   cudaEventCreate(&c->ev_clr);
   for (auto &e2 : c->ev_user) cudaEventCreate(&e2);
   cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&c->in_stream, cudaStreamNonBlocking);
   for (auto &e2 : c->ev_slice) cudaEventCreateWithFlags(&e2, cudaEventDisableTiming);
   cudaHostAlloc((void **)&c->h_slice_n, kSinkSlices * sizeof(unsigned long long), cudaHostAllocDefault);
   if ((e = dev_alloc(&c->d_ctr, 1)) != cudaSuccess) return bail(e, "cudaMalloc");
@@ -324,16 +334,31 @@ static void free_results(ResultSet &r) {
   r.sorted = false;
 }
 
+static void free_chunk(ReadChunk &ch) {
+  if (!ch.owner) return;
+  dev_free(ch.d_bytes);
+  dev_free(ch.d_offsets);
+  dev_free(ch.d_lens);
+}
+
 extern "C" int kc_clear_reads(kc_ctx *c) {
   if (!c) return KC_ERR_ARG;
   cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->in_stream);
   cudaStreamSynchronize(c->stream);
   for (auto &ch : c->chunks) {
-    dev_free(ch.d_bytes);
-    dev_free(ch.d_offsets);
-    dev_free(ch.d_lens);
+    if (!ch.owner) continue;
+    // keep the largest allocation for the next kc_add_reads (cudaMalloc / cudaFree of gigabytes are not free)
+    if (ch.cap_bytes > c->spare.cap_bytes && ch.cap_reads >= c->spare.cap_reads) {
+      free_chunk(c->spare);
+      c->spare = ch;
+      c->spare.owner = true;
+    } else {
+      free_chunk(ch);
+    }
   }
   c->chunks.clear();
+  c->ev_in_used = 0;
   c->n_reads = c->n_bases = 0;
   c->caps_valid = false;
   c->phase = PH_EMPTY;
@@ -343,6 +368,9 @@ extern "C" int kc_clear_reads(kc_ctx *c) {
 extern "C" void kc_destroy(kc_ctx *c) {
   if (!c) return;
   kc_clear_reads(c);
+  free_chunk(c->spare);
+  for (auto &e : c->ev_in_pool) cudaEventDestroy(e);
+  if (c->in_stream) cudaStreamDestroy(c->in_stream);
   dev_free(c->d_bins);
   dev_free(c->d_bin_base);
   dev_free(c->d_bin_first);
@@ -417,16 +445,68 @@ extern "C" int kc_add_reads(kc_ctx *c, const uint8_t *bytes, uint64_t n_bytes, c
   if (n_reads == 0) return KC_OK;
   CK(cudaSetDevice(c->device));
   ReadChunk ch;
-  ch.n_reads = n_reads;
-  ch.n_bytes = n_bytes;
-  CK(dev_alloc(&ch.d_bytes, n_bytes + 16));
-  CK(dev_alloc(&ch.d_offsets, n_reads));
-  CK(dev_alloc(&ch.d_lens, n_reads));
+  if (c->spare.d_bytes && c->spare.cap_bytes >= n_bytes + 16 && c->spare.cap_reads >= n_reads) {
+    ch = c->spare;
+    c->spare = ReadChunk();
+  } else {
+    ch.cap_bytes = n_bytes + 16;
+    ch.cap_reads = n_reads;
+    CK(dev_alloc(&ch.d_bytes, ch.cap_bytes));
+    CK(dev_alloc(&ch.d_offsets, n_reads));
+    CK(dev_alloc(&ch.d_lens, n_reads));
+  }
+  ch.owner = true;
   // cudaMemcpyDefault: host (pageable or pinned) and device sources alike
-  CK(cudaMemcpyAsync(ch.d_bytes, bytes, n_bytes, cudaMemcpyDefault, c->stream));
-  CK(cudaMemcpyAsync(ch.d_offsets, offsets, n_reads * sizeof(uint64_t), cudaMemcpyDefault, c->stream));
-  CK(cudaMemcpyAsync(ch.d_lens, lens, n_reads * sizeof(uint16_t), cudaMemcpyDefault, c->stream));
-  c->chunks.push_back(ch);
+  CK(cudaMemcpyAsync(ch.d_offsets, offsets, n_reads * sizeof(uint64_t), cudaMemcpyDefault, c->in_stream));
+  CK(cudaMemcpyAsync(ch.d_lens, lens, n_reads * sizeof(uint16_t), cudaMemcpyDefault, c->in_stream));
+  auto next_event = [&](cudaEvent_t *ev) -> cudaError_t {
+    if (c->ev_in_used == c->ev_in_pool.size()) {
+      cudaEvent_t e;
+      cudaError_t rc = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+      if (rc != cudaSuccess) return rc;
+      c->ev_in_pool.push_back(e);
+    }
+    *ev = c->ev_in_pool[c->ev_in_used++];
+    return cudaSuccess;
+  };
+  // A host source is copied in sub-chunks of whole reads, each with its own event. That needs the reads to lie in the
+  // byte buffer in order (offsets ascending, no overlap: the PackedReads layout); the check runs just ahead of the copies
+  // and everything after the first violation becomes one chunk.
+  cudaPointerAttributes at;
+  bool host_src = true;
+  if (cudaPointerGetAttributes(&at, bytes) == cudaSuccess && (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged)) host_src = false;
+  cudaGetLastError();
+  cudaPointerAttributes at2;
+  if (cudaPointerGetAttributes(&at2, offsets) == cudaSuccess && (at2.type == cudaMemoryTypeDevice || at2.type == cudaMemoryTypeManaged)) host_src = false;
+  cudaGetLastError();
+  uint64_t sub_bytes = 128ull << 20;
+  if (const char *e = getenv("KC_INPUT_CHUNK_BYTES")) sub_bytes = std::max<uint64_t>(strtoull(e, nullptr, 10), 4096);  // (tests)
+  uint64_t n_sub = host_src ? std::min<uint64_t>(std::max<uint64_t>(n_bytes / sub_bytes, 1), 32) : 1;
+  if (n_reads < 64 * n_sub) n_sub = 1;
+  uint64_t r0 = 0, b0 = 0;
+  for (uint64_t j = 0; j < n_sub && r0 < n_reads; j++) {
+    uint64_t r1 = n_reads * (j + 1) / n_sub;
+    bool ordered = true;
+    if (n_sub > 1) {
+      if (offsets[r0] < b0) ordered = false;
+      for (uint64_t r = r0; ordered && r + 1 < n_reads && r < r1; r++) ordered = offsets[r + 1] >= offsets[r] + lens[r];
+    }
+    if (!ordered || j + 1 == n_sub) r1 = n_reads;
+    const uint64_t b1 = r1 == n_reads ? n_bytes : offsets[r1];
+    const uint64_t lo = ordered ? b0 : 0;  // out of order: copy everything (again) before these reads are touched
+    CK(cudaMemcpyAsync(ch.d_bytes + lo, bytes + lo, (ordered ? b1 : n_bytes) - lo, cudaMemcpyDefault, c->in_stream));
+    ReadChunk sub = ch;
+    sub.owner = j == 0;
+    sub.d_offsets = ch.d_offsets + r0;
+    sub.d_lens = ch.d_lens + r0;
+    sub.n_reads = r1 - r0;
+    sub.n_bytes = b1 > b0 ? b1 - b0 : 0;
+    CK(next_event(&sub.ready));
+    CK(cudaEventRecord(sub.ready, c->in_stream));
+    c->chunks.push_back(sub);
+    r0 = r1;
+    b0 = b1;
+  }
   c->n_reads += n_reads;
   c->n_bases += n_bytes;
   c->caps_valid = false;
@@ -463,13 +543,13 @@ static ParseParams parse_params(kc_ctx *c, const ReadChunk &ch, uint32_t stride,
 // Lay the bins out on the device: per owner [header block][bin 0 records][bin 1 records]..., capacities from the
 // cursors of a counting pass (stride > 1: a strided sample, scaled with a noise margin; stride == 1: exact). Only the
 // per-owner region offsets / sizes (n_ranks values) come back to the host.
-static int layout_bins(kc_ctx *c, uint32_t stride) {
+static int layout_bins(kc_ctx *c, double scale) {
   const uint32_t n = c->n_ids;
   LayoutParams lp;
   memset(&lp, 0, sizeof lp);
   lp.n_ranks = (uint32_t)c->G;
   lp.local_bins = (uint32_t)c->P;
-  lp.stride = stride;
+  lp.scale = scale;
   lp.rec_bytes = c->rec_bytes;
   lp.header_bytes = c->header_bytes;
   lp.pad = 64;
@@ -539,14 +619,36 @@ static int estimate_caps(kc_ctx *c) {
     const double per_read = std::max(1.0, 2.0 * std::max(avg_len - c->k - 1, 0.0) / (double)(c->k - c->m + 2) + 1.0);
     want_reads = std::max<uint64_t>(want_reads, (uint64_t)(64.0 * n / per_read));
   }
-  uint32_t stride = (uint32_t)std::max<uint64_t>(1, c->n_reads / want_reads);
+  // Which reads to look at: every stride-th read of all chunks -- or, when the input arrives in several chunks (a host
+  // source is copied in sub-chunks), of the FIRST chunk only, so that the parse can start while the rest is still in
+  // flight. Reads come off a sequencer in no genomic order, so a prefix is as good a sample as a stride; if it is not, a
+  // bin overflows and kc_parse falls back to the exact layout.
+  size_t n_sample_chunks = c->chunks.size();
+  uint64_t pool = c->n_reads;
+  if (c->chunks.size() > 1) {
+    uint64_t have = 0;
+    for (size_t i = 0; i < c->chunks.size(); i++) {
+      have += c->chunks[i].n_reads;
+      if (have >= 2 * want_reads) {
+        n_sample_chunks = i + 1;
+        pool = have;
+        break;
+      }
+    }
+  }
+  uint32_t stride = (uint32_t)std::max<uint64_t>(1, pool / want_reads);
   CK(cudaMemsetAsync(c->d_cursor, 0, n * sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(&c->d_ctr->parse_counted, 0, 3 * sizeof(unsigned long long) + sizeof(unsigned int), c->stream));
-  for (auto &ch : c->chunks) {
+  uint64_t looked_at = 0;
+  for (size_t i = 0; i < n_sample_chunks; i++) {
+    const ReadChunk &ch = c->chunks[i];
+    if (ch.ready) CK(cudaStreamWaitEvent(c->stream, ch.ready, 0));
     ParseParams p = parse_params(c, ch, stride, 1);
     CK(launch_parse(p, c->sm_count, c->stream, &c->launches));
+    looked_at += (ch.n_reads + stride - 1) / stride;
   }
-  rc = layout_bins(c, stride);
+  const double scale = looked_at && looked_at < c->n_reads ? (double)c->n_reads / (double)looked_at : 1.0;
+  rc = layout_bins(c, scale);
   if (rc) return rc;
   c->caps_valid = true;
   return KC_OK;
@@ -560,6 +662,7 @@ static int run_parse(kc_ctx *c) {
   CK(cudaMemsetAsync(&c->d_ctr->parse_counted, 0, 3 * sizeof(unsigned long long) + sizeof(unsigned int), c->stream));
   CK(cudaEventRecord(c->ev_pk0, c->stream));
   for (auto &ch : c->chunks) {
+    if (ch.ready) CK(cudaStreamWaitEvent(c->stream, ch.ready, 0));
     ParseParams p = parse_params(c, ch, 1, 0);
     CK(launch_parse(p, c->sm_count, c->stream, &c->launches));
   }
@@ -600,7 +703,7 @@ extern "C" int kc_parse(kc_ctx *c) {
       fprintf(stderr, "[kc] %llu of %u bins overflowed; %llu records, capacity %llu\n", (unsigned long long)n_over, c->n_ids,
               (unsigned long long)sum, (unsigned long long)sumcap);
     }
-    rc = layout_bins(c, 1);
+    rc = layout_bins(c, 1.0);
     if (rc) return rc;
     rc = run_parse(c);
     if (rc) return rc;

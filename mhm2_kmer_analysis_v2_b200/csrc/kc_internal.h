@@ -142,7 +142,8 @@ cudaError_t launch_write_headers(uint8_t *const *dst_header, const uint64_t *bin
                                  uint64_t *launches);
 // bin layout computed on the device from the cursors of a (sampled) counting pass
 struct LayoutParams {
-  uint32_t n_ranks, local_bins, stride;
+  uint32_t n_ranks, local_bins;
+  double scale;                           // all reads / reads the counting pass looked at (1 = exact)
   int rec_bytes, header_bytes;
   unsigned long long pad;                 // records added to every bin
   const unsigned long long *bin_cursor;   // [n_ids] records seen by the counting pass

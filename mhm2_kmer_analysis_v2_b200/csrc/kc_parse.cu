@@ -407,12 +407,12 @@ __global__ void __launch_bounds__(1024) layout_caps_kernel(LayoutParams p) {
   unsigned long long cap = 0;
   if (b < P) {
     const double cnt = (double)p.bin_cursor[o * P + b];
-    double est = cnt * p.stride;
-    if (p.stride > 1) {
-      est += 7.0 * p.stride * sqrt(cnt + 1.0) + 0.03 * est;  // sampling noise of a strided sample
+    double est = cnt * p.scale;
+    if (p.scale > 1.0) {
+      est += 7.0 * p.scale * sqrt(cnt + 1.0) + 0.03 * est;  // sampling noise of the sample
       // bins are filled by a hash, so a bin whose sample came out far BELOW the average is most likely just unlucky:
       // never go under 1.25 x the average bin (a 7-sigma margin on 3 sampled records is no protection at all)
-      const double avg = (double)*p.sampled_total * p.stride / ((double)P * p.n_ranks);
+      const double avg = (double)*p.sampled_total * p.scale / ((double)P * p.n_ranks);
       if (est < 1.25 * avg) est = 1.25 * avg;
     }
     cap = (unsigned long long)est + p.pad;

@@ -116,3 +116,20 @@ def test_result_sink_streams_the_survivors(oracle_mod, k, bins):
         st2.run()
     st.close()
     st2.close()
+
+
+@pytest.mark.parametrize("order", ["ascending", "shuffled"])
+def test_chunked_input_copies(oracle_mod, monkeypatch, order):
+    """A host source is copied in sub-chunks (own events, parse starts on the first one, bin capacities sampled from it);
+    reads that do not lie in the byte buffer in order fall back to one chunk."""
+    monkeypatch.setenv("KC_INPUT_CHUNK_BYTES", "65536")
+    k = 33
+    reads = K.generate(None, 12_000, seed=777, **SMALL)
+    if order == "shuffled":
+        perm = np.random.default_rng(5).permutation(len(reads))
+        reads = K.ReadSet(reads.bytes, reads.offsets[perm].copy(), reads.lens[perm].copy())
+    o = oracle_run(oracle_mod, reads, k)
+    st, stats = gpu_single(reads, k)
+    assert stats["inserted_kmers"] == reads.counted_kmers(k)
+    assert_same(st.result(True), o.result(True), f"chunked input, {order}")
+    st.close()
