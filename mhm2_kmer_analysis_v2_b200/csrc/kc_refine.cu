@@ -17,7 +17,7 @@
 
 namespace kc {
 
-static const int RF_THREADS = 256;
+static const int RF_THREADS = 512;
 static const int RF_MAX_SUB = 256;
 static const int RF_STAGE_BYTES = 96 * 1024;  // records of a coarse bin held in shared memory (larger bins are re-read from L2)
 
@@ -129,14 +129,29 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(RefineParams p) {
     if (staged) {
       uint4 *st4 = reinterpret_cast<uint4 *>(s_stage);
       const uint32_t n16 = n * U;
-      for (uint32_t u = tid; u < n16; u += RF_THREADS) {
-        const uint32_t r = u / U;
-        int s = 0;
-        while (s_seg_start[s + 1] <= r) s++;
-        const uint4 *g = reinterpret_cast<const uint4 *>(s_seg_ptr[s] + (uint64_t)(r - s_seg_start[s]) * R);
-        const uint4 v = ld_stream16(g + (u % U));
-        st4[u] = v;
-        if ((int)(u % U) == U - 1) atomicAdd(&s_cnt[(v.w >> 8) & (F - 1u)], 1u);
+      // four loads in flight per thread before the first one is consumed
+      for (uint32_t u0 = tid; u0 < n16; u0 += 4 * RF_THREADS) {
+        uint4 v[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          const uint32_t u = u0 + q * RF_THREADS;
+          if (u < n16) {
+            const uint32_t r = u / U;
+            int s = 0;
+            if (p.n_src > 1)
+              while (s_seg_start[s + 1] <= r) s++;
+            const uint4 *g = reinterpret_cast<const uint4 *>(s_seg_ptr[s] + (uint64_t)(r - s_seg_start[s]) * R);
+            v[q] = ld_stream16(g + (u % U));
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          const uint32_t u = u0 + q * RF_THREADS;
+          if (u < n16) {
+            st4[u] = v[q];
+            if ((int)(u % U) == U - 1) atomicAdd(&s_cnt[(v[q].w >> 8) & (F - 1u)], 1u);
+          }
+        }
       }
     } else {
       for (uint32_t r = tid; r < n; r += RF_THREADS) {
