@@ -35,9 +35,10 @@ namespace kc {
 
 static const int CW_WARPS = 4;        // warps per CTA (independent of each other)
 static const int CW_THREADS = CW_WARPS * 32;
-static const int CW_CTAS_PER_SM = 4;  // 12 warps per SM: the kernel is issue-bound, the table size matters more than occupancy
+static const int CW_CTAS_PER_SM = 5;  // 20 warps per SM (measured: 12 -> 54 ms, 16 -> 48, 20 -> 45.6, 24 -> 48.7 on C2; more warps hide latency, fewer mean larger tables and fewer bins)
+static const int CW_ILP = 1;          // k-mer occurrences per lane and step (independent instruction streams hide latency)
 static const int CW_STACK = 16;       // pending (split, residue) parts of a bin
-static const int CW_TMAX = 4096;      // k-mer occurrences per staged chunk (bits of the record-start bitmap)
+static const int CW_TMAX = 3072;      // k-mer occurrences per staged chunk (bits of the record-start bitmap)
 static const uint32_t C_PENDING = 0xfffffffcu;
 static const uint32_t C_NOT_FOUND = 0xffffffffu;
 static const uint32_t C_SKIP = 0xfffffffdu;
@@ -60,21 +61,22 @@ static inline size_t count_slot_bytes(int n_words) { return 24 + 8 * (size_t)n_w
 __host__ __device__ inline CountGeom count_geom(int n_words, int rec_bytes, int k, int warp_bytes) {
   CountGeom g;
   const int max_kmers = record_geom(rec_bytes, k).max_kmers;
-  int cap = rec_bytes == 64 ? 64 : 96;
+  int cap = rec_bytes == 64 ? 32 : 64;
   if (cap * max_kmers > CW_TMAX) cap = CW_TMAX / (max_kmers > 0 ? max_kmers : 1);
   if (cap < 1) cap = 1;
   g.cap_rec = cap;
-  g.stage_bytes = (rec_bytes == 64 ? 64 : 96) * rec_bytes;
-  if (g.stage_bytes < 1536) g.stage_bytes = 1536;
+  g.stage_bytes = (rec_bytes == 64 ? 32 : 64) * rec_bytes;
+  if (g.stage_bytes < 1024) g.stage_bytes = 1024;  // (the sweep keeps its list of u16 slot numbers here)
   g.off_pre = g.stage_bytes;                 // u16 [cap + 1]
-  g.off_bitmap = g.off_pre + 208;            // u32 [CW_TMAX / 32]
+  g.off_bitmap = g.off_pre + 144;            // u32 [CW_TMAX / 32]
   g.off_nz = g.off_bitmap + CW_TMAX / 8;     // u8 [cap]
-  g.off_stack = g.off_nz + 96;               // u32 [CW_STACK]
+  g.off_stack = g.off_nz + 64;               // u32 [CW_STACK]
   g.off_heavy = g.off_stack + CW_STACK * 4;  // u32 slot[kCountMaxHeavy], u32 side[kCountMaxHeavy * 8]
   g.off_table = g.off_heavy + kCountMaxHeavy * 36;
   g.off_table = (g.off_table + 15) & ~15;
   const int avail = warp_bytes - g.off_table;
   uint32_t s = avail > 0 ? (uint32_t)(avail / (24 + 8 * n_words)) : 0u;
+  if (s > (uint32_t)g.stage_bytes / 2u) s = (uint32_t)g.stage_bytes / 2u;  // the sweep's list lives in the record stage
   g.slots = s & ~3u;
   g.warp_bytes = warp_bytes;
   return g;
@@ -146,63 +148,81 @@ __device__ __forceinline__ bool key_equals(const uint64_t *slot_key, const uint6
 //   * a lane that loses the CAS for an empty slot looks at the same bucket again in the next round and then finds the
 //     winner's key (maybe its own key: equal keys racing for a bucket see the same tags and pick the same slot).
 // Returns the slot, C_NOT_FOUND (find-only miss, or no room: `full` set) or C_SKIP (!mine).
-template <int N, bool CLAIM>
-__device__ __forceinline__ uint32_t probe_warp(const Table<N> &tb, const uint64_t (&key)[N], uint64_t h, bool mine, bool &is_new, bool &full) {
-  const uint32_t fp = (uint32_t)(h >> 32) | 1u;
+// ILP keys per lane go through the rounds together (their loads and compares interleave in the instruction stream: the
+// kernel is latency-bound, not issue-bound). Per round: all tag loads, then all key compares, then all claims -- so the
+// argument above holds across the ILP keys as well (a claim of this round is never seen by a tag load of this round).
+template <int N, bool CLAIM, int ILP>
+__device__ __forceinline__ void probe_warp(const Table<N> &tb, const uint64_t (&key)[ILP][N], const uint64_t (&h)[ILP], const bool (&mine)[ILP],
+                                           uint32_t (&slot)[ILP], bool (&is_new)[ILP], bool &full) {
   const uint32_t nb = tb.n_slots >> 2;
-  uint32_t b = __umulhi((uint32_t)h, nb);
-  uint32_t slot = mine ? C_PENDING : C_SKIP;
-  uint32_t probes = 0;
-  is_new = false;
-  while (__any_sync(0xffffffffu, slot == C_PENDING)) {
-    if (slot == C_PENDING) {
-      const uint4 v = lds_volatile16(tb.tag + 4 * b);
-      const bool m0 = v.x == fp, m1 = v.y == fp, m2 = v.z == fp, m3 = v.w == fp;
-      if (m0 || m1 || m2 || m3) {
+  uint32_t fp[ILP], b[ILP], probes[ILP];
+#pragma unroll
+  for (int u = 0; u < ILP; u++) {
+    fp[u] = (uint32_t)(h[u] >> 32) | 1u;
+    b[u] = __umulhi((uint32_t)h[u], nb);
+    slot[u] = mine[u] ? C_PENDING : C_SKIP;
+    probes[u] = 0;
+    is_new[u] = false;
+  }
+  while (true) {
+    bool pending = false;
+#pragma unroll
+    for (int u = 0; u < ILP; u++) pending = pending || slot[u] == C_PENDING;
+    if (!__any_sync(0xffffffffu, pending)) break;
+    uint4 v[ILP];
+#pragma unroll
+    for (int u = 0; u < ILP; u++) v[u] = lds_volatile16(tb.tag + 4 * b[u]);  // (lanes that are done re-read their last bucket: harmless)
+    // ---- lookups
+#pragma unroll
+    for (int u = 0; u < ILP; u++) {
+      const bool m0 = v[u].x == fp[u], m1 = v[u].y == fp[u], m2 = v[u].z == fp[u], m3 = v[u].w == fp[u];
+      if (slot[u] == C_PENDING && (m0 || m1 || m2 || m3)) {
         const int jm = m0 ? 0 : (m1 ? 1 : (m2 ? 2 : 3));
-        if (key_equals<N>(tb.key + (size_t)(4 * b + jm) * N, key)) {
-          slot = 4 * b + jm;
+        if (key_equals<N>(tb.key + (size_t)(4 * b[u] + jm) * N, key[u])) {
+          slot[u] = 4 * b[u] + jm;
         } else {
           // another key with the same 32-bit fingerprint in this bucket (about once in 10^9 lookups): check the rest
-          const uint32_t tv[4] = {v.x, v.y, v.z, v.w};
+          const uint32_t tv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
           for (int j = 1; j < 4; j++)
-            if (j > jm && slot == C_PENDING && tv[j] == fp && key_equals<N>(tb.key + (size_t)(4 * b + j) * N, key)) slot = 4 * b + j;
+            if (j > jm && slot[u] == C_PENDING && tv[j] == fp[u] && key_equals<N>(tb.key + (size_t)(4 * b[u] + j) * N, key[u])) slot[u] = 4 * b[u] + j;
         }
       }
-      if (slot == C_PENDING) {
+    }
+    // ---- claims
+#pragma unroll
+    for (int u = 0; u < ILP; u++) {
+      if (slot[u] == C_PENDING) {
         // first empty slot, starting at a fingerprint-dependent position so that different new keys of a bucket rarely
         // fight for the same slot (equal keys still pick the same one)
-        const uint32_t r = (fp >> 1) & 3u;
-        const bool e0 = v.x == 0u, e1 = v.y == 0u, e2 = v.z == 0u, e3 = v.w == 0u;
-        const uint32_t em = (uint32_t)e0 | ((uint32_t)e1 << 1) | ((uint32_t)e2 << 2) | ((uint32_t)e3 << 3);
+        const uint32_t r = (fp[u] >> 1) & 3u;
+        const uint32_t em = (uint32_t)(v[u].x == 0u) | ((uint32_t)(v[u].y == 0u) << 1) | ((uint32_t)(v[u].z == 0u) << 2) | ((uint32_t)(v[u].w == 0u) << 3);
         if (em) {
           if (!CLAIM) {
-            slot = C_NOT_FOUND;
+            slot[u] = C_NOT_FOUND;
           } else {
             const uint32_t rot = ((em | (em << 4)) >> r) & 0xfu;  // bit t = slot (r + t) & 3 is empty
-            const uint32_t i = 4 * b + ((r + (uint32_t)__ffs(rot) - 1u) & 3u);
-            if (atomicCAS(tb.tag + i, 0u, fp) == 0u) {
+            const uint32_t i = 4 * b[u] + ((r + (uint32_t)__ffs(rot) - 1u) & 3u);
+            if (atomicCAS(tb.tag + i, 0u, fp[u]) == 0u) {
 #pragma unroll
-              for (int w = 0; w < N; w++) *reinterpret_cast<volatile uint64_t *>(tb.key + (size_t)i * N + w) = key[w];
-              is_new = true;
-              slot = i;
+              for (int w = 0; w < N; w++) *reinterpret_cast<volatile uint64_t *>(tb.key + (size_t)i * N + w) = key[u][w];
+              is_new[u] = true;
+              slot[u] = i;
             }
             // else: somebody else took that slot in this round (maybe with this very key): look at the bucket again
           }
         } else {
-          b++;
-          if (b == nb) b = 0;
-          if (++probes >= min(nb, 8u)) {  // a chain of full buckets: the table is (as good as) full
+          b[u]++;
+          if (b[u] == nb) b[u] = 0;
+          if (++probes[u] >= min(nb, 8u)) {  // a chain of full buckets: the table is (as good as) full
             full = true;
-            slot = C_NOT_FOUND;
+            slot[u] = C_NOT_FOUND;
           }
         }
       }
     }
     __syncwarp();
   }
-  return slot;
 }
 
 // ------------------------------------------------------------------------------------------------ per-warp state
@@ -227,10 +247,10 @@ __device__ __forceinline__ uint32_t stage_chunk(const CountParams &p, WarpCtx &w
   constexpr int W = R / 4;
   constexpr int U = R / 16;
   const uint32_t lane = lane_id();
-  // clear the bitmap (CW_TMAX / 32 = 128 words)
+  // clear the bitmap (CW_TMAX / 32 words)
   {
     uint4 *bm = reinterpret_cast<uint4 *>(wc.s_bitmap);
-    bm[lane] = make_uint4(0u, 0u, 0u, 0u);
+    if (lane < CW_TMAX / 128) bm[lane] = make_uint4(0u, 0u, 0u, 0u);
   }
   __syncwarp();
   uint32_t run = 0, rank0 = 0;
@@ -288,8 +308,8 @@ __device__ __forceinline__ uint32_t stage_chunk(const CountParams &p, WarpCtx &w
   return run;
 }
 
-// One staged chunk: all lanes walk its occurrences, 32 per step.
-template <int N, int R, bool HEAVY>
+// One staged chunk: all lanes walk its occurrences, 32 * ILP per step (lane l takes occurrences q0 + 32 u + l).
+template <int N, int R, bool HEAVY, int ILP>
 __device__ __forceinline__ void walk_chunk(const CountParams &p, const Table<N> &tb, WarpCtx &wc, uint32_t total, uint32_t n_rank,
                                            uint32_t &claimed, bool &overflow) {
   constexpr int W = R / 4;
@@ -304,70 +324,85 @@ __device__ __forceinline__ void walk_chunk(const CountParams &p, const Table<N> 
   const int rsh = 2 * (15 - ((k + 1) & 15));
   const uint32_t le_mask = 0xffffffffu >> (31u - lane);
   uint32_t rank_run = 0;
-  for (uint32_t q0 = 0; q0 < total; q0 += 32) {
-    const uint32_t bits = wc.s_bitmap[q0 >> 5];
-    const uint32_t q = q0 + lane;
-    const bool active = q < total;
-    uint32_t rank = rank_run + (uint32_t)__popc(bits & le_mask) - 1u;
-    rank_run += (uint32_t)__popc(bits);
-    if (rank >= n_rank) rank = n_rank - 1u;  // lanes past the end
-    const uint32_t ri = wc.s_nz[rank];
-    const int j = active ? (int)(q - wc.s_pre[rank]) : 0;
-    const uint32_t *rec = wc.s_rec + ri * W;
-    // ---- window of k + 2 bases starting at base j (left extension, k-mer, right extension)
-    const int a = j >> 4, s = (j & 15) * 2;
-    uint32_t wd[2 * N + 1];
+  for (uint32_t q0 = 0; q0 < total; q0 += 32 * ILP) {
+    uint64_t key[ILP][N], h[ILP];
+    uint32_t el[ILP], er[ILP];
+    bool mine[ILP];
 #pragma unroll
-    for (int i = 0; i < 2 * N; i++) wd[i] = rec[a + i];
-    wd[2 * N] = rec[min(a + 2 * N, W - 1)];
-    uint32_t x[2 * N + 1];
+    for (int u = 0; u < ILP; u++) {
+      const uint32_t qb = q0 + 32u * u;
+      const uint32_t bits = qb < total ? wc.s_bitmap[qb >> 5] : 0u;
+      const uint32_t q = qb + lane;
+      const bool active = q < total;
+      uint32_t rank = rank_run + (uint32_t)__popc(bits & le_mask) - 1u;
+      rank_run += (uint32_t)__popc(bits);
+      if (rank >= n_rank) rank = n_rank - 1u;  // lanes past the end
+      const uint32_t ri = wc.s_nz[rank];
+      const int j = active ? (int)(q - wc.s_pre[rank]) : 0;
+      const uint32_t *rec = wc.s_rec + ri * W;
+      // ---- window of k + 2 bases starting at base j (left extension, k-mer, right extension)
+      const int a = j >> 4, s = (j & 15) * 2;
+      uint32_t wd[2 * N + 1];
 #pragma unroll
-    for (int i = 0; i < 2 * N; i++) x[i] = __funnelshift_l(wd[i + 1], wd[i], s);
-    x[2 * N] = wd[2 * N] << s;
-    const uint32_t lb = x[0] >> 30;
-    const uint32_t rbw = rw == 2 * N - 2 ? x[2 * N - 2] : (rw == 2 * N - 1 ? x[2 * N - 1] : x[2 * N]);
-    const uint32_t rb = (rbw >> rsh) & 3u;
-    const uint32_t lq = (rec[NBW + (j >> 5)] >> (31 - (j & 31))) & 1u;
-    const int jr = j + k + 1;
-    const uint32_t rq = (rec[NBW + (jr >> 5)] >> (31 - (jr & 31))) & 1u;
-    uint64_t fw[N], rc[N], key[N];
+      for (int i = 0; i < 2 * N; i++) wd[i] = rec[a + i];
+      wd[2 * N] = rec[min(a + 2 * N, W - 1)];
+      uint32_t x[2 * N + 1];
 #pragma unroll
-    for (int i = 0; i < N; i++) {
-      const uint32_t hi = __funnelshift_l(x[2 * i + 1], x[2 * i], 2), lo = __funnelshift_l(x[2 * i + 2], x[2 * i + 1], 2);
-      fw[i] = ((uint64_t)hi << 32) | lo;
-    }
-    fw[N - 1] &= last_mask;
-    revcomp_key<N>(fw, k, rc);
-    const bool sw = key_less<N>(rc, fw);  // kcount_cpu.cpp:328-333: swap and complement the extensions
+      for (int i = 0; i < 2 * N; i++) x[i] = __funnelshift_l(wd[i + 1], wd[i], s);
+      x[2 * N] = wd[2 * N] << s;
+      const uint32_t lb = x[0] >> 30;
+      const uint32_t rbw = rw == 2 * N - 2 ? x[2 * N - 2] : (rw == 2 * N - 1 ? x[2 * N - 1] : x[2 * N]);
+      const uint32_t rb = (rbw >> rsh) & 3u;
+      const uint32_t lq = (rec[NBW + (j >> 5)] >> (31 - (j & 31))) & 1u;
+      const int jr = j + k + 1;
+      const uint32_t rq = (rec[NBW + (jr >> 5)] >> (31 - (jr & 31))) & 1u;
+      uint64_t fw[N], rc[N];
 #pragma unroll
-    for (int i = 0; i < N; i++) key[i] = sw ? rc[i] : fw[i];
-    // extension letters with their "counts" flag in bit 2; reverse strand: swapped and complemented
-    const uint32_t la = lb | (lq << 2), ra = rb | (rq << 2);
-    const uint32_t el = sw ? (ra ^ 3u) : la, er = sw ? (la ^ 3u) : ra;
-    const uint64_t h = count_hash<N>(key);
-    const bool mine = active && (((uint32_t)(h >> 48) & wc.split_mask) == wc.split_res);  // else: another part of a split bin
-    bool is_new, full = false;
-    if (!HEAVY) {
-      const uint32_t slot = probe_warp<N, true>(tb, key, h, mine, is_new, full);
-      if (slot < C_PENDING) {
-        uint32_t *e = tb.ext + slot;
-        atomicAdd(tb.cnt + slot, 1u);
-        if (el & 4u) atomicAdd(e + ((el & 2u) ? S : 0u), 1u << ((el & 1u) << 4));
-        if (er & 4u) atomicAdd(e + ((er & 2u) ? 3u * S : 2u * S), 1u << ((er & 1u) << 4));
+      for (int i = 0; i < N; i++) {
+        const uint32_t hi = __funnelshift_l(x[2 * i + 1], x[2 * i], 2), lo = __funnelshift_l(x[2 * i + 2], x[2 * i + 1], 2);
+        fw[i] = ((uint64_t)hi << 32) | lo;
       }
-      claimed += is_new;  // (per lane; summed over the warp at the end of the chunk)
+      fw[N - 1] &= last_mask;
+      revcomp_key<N>(fw, k, rc);
+      const bool sw = key_less<N>(rc, fw);  // kcount_cpu.cpp:328-333: swap and complement the extensions
+#pragma unroll
+      for (int i = 0; i < N; i++) key[u][i] = sw ? rc[i] : fw[i];
+      // extension letters with their "counts" flag in bit 2; reverse strand: swapped and complemented
+      const uint32_t la = lb | (lq << 2), ra = rb | (rq << 2);
+      el[u] = sw ? (ra ^ 3u) : la;
+      er[u] = sw ? (la ^ 3u) : ra;
+      h[u] = count_hash<N>(key[u]);
+      mine[u] = active && (((uint32_t)(h[u] >> 48) & wc.split_mask) == wc.split_res);  // else: another part of a split bin
+    }
+    uint32_t slot[ILP];
+    bool is_new[ILP], full = false;
+    if (!HEAVY) {
+      probe_warp<N, true, ILP>(tb, key, h, mine, slot, is_new, full);
+#pragma unroll
+      for (int u = 0; u < ILP; u++) {
+        if (slot[u] < C_PENDING) {
+          uint32_t *e = tb.ext + slot[u];
+          atomicAdd(tb.cnt + slot[u], 1u);
+          if (el[u] & 4u) atomicAdd(e + ((el[u] & 2u) ? S : 0u), 1u << ((el[u] & 1u) << 4));
+          if (er[u] & 4u) atomicAdd(e + ((er[u] & 2u) ? 3u * S : 2u * S), 1u << ((er[u] & 1u) << 4));
+        }
+        claimed += is_new[u];  // (per lane; summed over the warp at the end of the chunk)
+      }
       if (__any_sync(0xffffffffu, full)) {  // no room: the pass is abandoned and the bin is split
         overflow = true;
         break;
       }
     } else {  // exact 32-bit recount of the extensions of the keys listed as heavy
-      const uint32_t slot = probe_warp<N, false>(tb, key, h, mine, is_new, full);
-      if (slot < C_PENDING) {
-        const uint32_t c = tb.cnt[slot];
-        if (c & kHeavyMark) {
-          uint32_t *e = wc.s_heavy_side + (c & ~kHeavyMark) * 8;
-          if (el & 4u) atomicAdd(e + (el & 3u), 1u);
-          if (er & 4u) atomicAdd(e + 4 + (er & 3u), 1u);
+      probe_warp<N, false, ILP>(tb, key, h, mine, slot, is_new, full);
+#pragma unroll
+      for (int u = 0; u < ILP; u++) {
+        if (slot[u] < C_PENDING) {
+          const uint32_t c = tb.cnt[slot[u]];
+          if (c & kHeavyMark) {
+            uint32_t *e = wc.s_heavy_side + (c & ~kHeavyMark) * 8;
+            if (el[u] & 4u) atomicAdd(e + (el[u] & 3u), 1u);
+            if (er[u] & 4u) atomicAdd(e + 4 + (er[u] & 3u), 1u);
+          }
         }
       }
     }
@@ -386,7 +421,7 @@ __device__ __forceinline__ bool walk_bin(const CountParams &p, const Table<N> &t
     const uint32_t occ = stage_chunk<R>(p, wc, c0, (int)min((uint32_t)cap_rec, total - c0), n_nz);
     n_records += n_nz;
     n_occ += occ;
-    if (occ) walk_chunk<N, R, HEAVY>(p, tb, wc, occ, n_nz, claimed, overflow);
+    if (occ) walk_chunk<N, R, HEAVY, (HEAVY ? 1 : CW_ILP)>(p, tb, wc, occ, n_nz, claimed, overflow);
     // too full to go on efficiently (every lane counts its own claims)
     if (!HEAVY && !overflow && __reduce_add_sync(0xffffffffu, claimed) >= p.claim_limit) overflow = true;
   }
