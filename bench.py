@@ -212,6 +212,9 @@ def main():
     ap.add_argument("--cpu-sample-reads", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--exchange", default="pull", choices=["pull", "nccl"],
+                    help="multi-GPU: 'pull' = peers' bins mapped with CUDA IPC, the refine kernel reads them over NVLink; "
+                         "'nccl' = all-to-all of the owner regions, then refine")
     ap.add_argument("--n-genomes", type=int, default=0, help="profiling only: fewer genomes keep the coverage of a smaller read set like the full workload's")
     ap.add_argument("--phase-detail", action="store_true", help="also print per-phase device times to stderr")
     args = ap.parse_args()
@@ -242,7 +245,7 @@ def main():
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    from mhm2_kmer_analysis_v2_b200.exchange import exchange_supermers
+    from mhm2_kmer_analysis_v2_b200.exchange import exchange_supermers, exchange_supermers_pull, release_peers
 
     k, n = args.k, args.reads_per_gpu
     # ---- this rank's reads, generated straight into pinned host memory
@@ -279,9 +282,12 @@ def main():
         st.parse()
         xb = (0, 0, 0.0)
         if world > 1:
-            xb = exchange_supermers(st)
+            xb = exchange_supermers_pull(st) if args.exchange == "pull" else exchange_supermers(st)
         st.insert()
-        return st.finalize(), xb
+        fin = st.finalize()
+        if world > 1 and args.exchange == "pull":
+            release_peers(st)  # nobody parses again while a peer may still be reading this rank's bins
+        return fin, xb
 
     def max_over_ranks(x):
         if dist is None:
@@ -309,7 +315,7 @@ def main():
         stats, _ = one_pass()
     launches0 = st.stats()["kernel_launches"]
     phase = {"parse": 0.0, "parse_kernel": 0.0, "insert": 0.0, "insert_kernel": 0.0, "table_clear": 0.0, "finalize": 0.0, "exchange_s": 0.0}
-    xbytes = 0
+    xbytes = xpulled = 0
     barrier()
     st.timer_mark(0)
     for _ in range(args.steps):
@@ -318,6 +324,7 @@ def main():
             phase[name] += stats["ms_" + name]
         phase["exchange_s"] += xb[2]
         xbytes += xb[0]
+        xpulled += xb[1]
     st.timer_mark(1)
     barrier()
     ms_total = st.timer_elapsed_ms(0, 1)
@@ -331,6 +338,12 @@ def main():
     peak, peak_src = load_peaks()
     achieved = b_alg(k) * inserted / (ms_insert_kernel / 1e3) / 1e9
     final_local = stats["final_kmers"]
+    checksum_all = None
+    if dist is not None:  # order-independent result checksum, summed over the owners (mod 2^64): the same for any exchange mode
+        cs = st.checksum(False)
+        parts = [None] * world
+        dist.all_gather_object(parts, int(cs))
+        checksum_all = sum(parts) % (1 << 64)
 
     # ---- end-to-end arm: host reads in, host result out, through the C ABI
     e2e = None
@@ -417,9 +430,22 @@ def main():
         }
         if world > 1:
             xs = phase["exchange_s"] / args.steps
-            line["exchange"] = {"bytes_sent_per_gpu_per_step": xbytes / args.steps, "seconds": xs,
-                                "gbps_per_gpu_per_direction": (xbytes / args.steps) / xs / 1e9 if xs > 0 else None,
-                                "nvlink_peak_gbps": 900.0, "owner_imbalance": red.get("owner_imbalance") if red else None}
+            if args.exchange == "pull":
+                # the transfer happens inside the refine kernel: time = insert phase minus the count kernel
+                xs = (phase["insert"] - phase["insert_kernel"]) / args.steps / 1e3
+                rec_b = stats["supermer_bytes_out"] / max(stats["supermers_out"], 1)
+                # records that crossed NVLink: what this owner consumed minus its own share (owners are balanced by the hash)
+                xpulled = stats["supermers_in"] * rec_b * (world - 1) / world * args.steps
+                line["exchange"] = {"mode": "pull: refine kernel reads the peers' bins over NVLink (CUDA IPC), no staging",
+                                    "bytes_pulled_per_gpu_per_step_approx": xpulled / args.steps, "seconds_refine_incl_local_bins": xs,
+                                    "gbps_per_gpu_per_direction": (xpulled / args.steps) / xs / 1e9 if xs > 0 else None,
+                                    "nvlink_peak_gbps": 900.0, "owner_imbalance": red.get("owner_imbalance") if red else None}
+            else:
+                line["exchange"] = {"mode": "nccl all-to-all of owner regions (slack between bins travels too)",
+                                    "bytes_sent_per_gpu_per_step": xbytes / args.steps, "seconds": xs,
+                                    "gbps_per_gpu_per_direction": (xbytes / args.steps) / xs / 1e9 if xs > 0 else None,
+                                    "nvlink_peak_gbps": 900.0, "owner_imbalance": red.get("owner_imbalance") if red else None}
+            line["table"]["checksum_sum_over_ranks"] = checksum_all
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()

@@ -154,6 +154,19 @@ int kc_exchange_recv_buffer(kc_ctx *ctx, const uint64_t *recv_bytes /* [n_ranks]
 /* byte offset of each source rank's block inside the receive buffer (256-byte aligned) */
 int kc_exchange_recv_offsets(kc_ctx *ctx, uint64_t *offsets /* [n_ranks] */);
 int kc_exchange_done(kc_ctx *ctx);
+/* Peer-memory exchange (ranks = GPUs of one NVLink / NVSwitch node). Instead of moving every owner's buffer with an
+ * all-to-all and then partitioning it, a rank EXPORTS its send buffer (CUDA IPC handle + the offset / used bytes of every
+ * owner's region in it), every owner IMPORTS the regions meant for it, and kc_insert's refine kernel pulls the records
+ * straight out of the peers' HBM over NVLink while it sorts them into fine bins: one kernel does the transfer and the
+ * partition, only used records cross the links, nothing is staged. Replaces the same reference calls as the block
+ * above (KmerDHT::add_supermer / flush_updates, src/kcount/kmer_dht.cpp:248-258).
+ * Protocol: kc_parse on every rank, a barrier; kc_exchange_export; all-gather of (handle, offsets, bytes);
+ * kc_exchange_import for every other rank; kc_exchange_done; kc_insert; kc_finalize; a barrier before the next kc_parse /
+ * kc_reset / kc_add_reads of any rank (peers may still be reading this rank's buffer until their kc_finalize returns). */
+#define KC_IPC_HANDLE_BYTES 64
+int kc_exchange_export(kc_ctx *ctx, uint8_t *handle /* [KC_IPC_HANDLE_BYTES] */, uint64_t *region_offsets /* [n_ranks] */,
+                       uint64_t *region_bytes /* [n_ranks] */);
+int kc_exchange_import(kc_ctx *ctx, int src_rank, const uint8_t *handle, uint64_t region_offset, uint64_t region_bytes);
 /* (3)+(4) insert every received supermer's k-mers into the table (through the filter when enabled). */
 int kc_insert(kc_ctx *ctx);
 /* (5) purge count<2, resolve extensions, compact survivors. Synchronises and fills stats. */

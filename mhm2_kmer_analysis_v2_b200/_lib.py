@@ -70,6 +70,8 @@ PROTOTYPES = {
     "kc_exchange_recv_buffer": (C.c_int, [vp, vp, C.POINTER(vp)]),
     "kc_exchange_recv_offsets": (C.c_int, [vp, vp]),
     "kc_exchange_done": (C.c_int, [vp]),
+    "kc_exchange_export": (C.c_int, [vp, vp, vp, vp]),
+    "kc_exchange_import": (C.c_int, [vp, C.c_int, vp, C.c_uint64, C.c_uint64]),
     "kc_insert": (C.c_int, [vp]),
     "kc_finalize": (C.c_int, [vp, C.POINTER(KcStats)]),
     "kc_run": (C.c_int, [vp, C.POINTER(KcStats)]),

@@ -94,6 +94,8 @@ struct kc_ctx {
   bool caps_valid = false;
 
   // receive side
+  std::vector<uint8_t *> pull_ptr;                         // peer-memory exchange: region of source s in ITS memory (IPC-mapped)
+  std::vector<std::pair<std::string, void *>> ipc_mapped;  // opened IPC handles (raw bytes -> base pointer)
   uint8_t *d_recv = nullptr;
   uint64_t recv_alloc = 0;
   std::vector<uint64_t> recv_off, recv_bytes;
@@ -368,6 +370,7 @@ extern "C" int kc_clear_reads(kc_ctx *c) {
 extern "C" void kc_destroy(kc_ctx *c) {
   if (!c) return;
   kc_clear_reads(c);
+  for (auto &m : c->ipc_mapped) cudaIpcCloseMemHandle(m.second);
   free_chunk(c->spare);
   for (auto &e : c->ev_in_pool) cudaEventDestroy(e);
   if (c->in_stream) cudaStreamDestroy(c->in_stream);
@@ -725,6 +728,7 @@ extern "C" int kc_parse(kc_ctx *c) {
   c->stats.supermer_bytes_out = c->h_ctr.parse_records * c->rec_bytes;
   c->phase = PH_PARSED;
   c->recv_off.clear();
+  c->pull_ptr.clear();
   return KC_OK;
 }
 
@@ -753,6 +757,7 @@ extern "C" int kc_exchange_recv_buffer(kc_ctx *c, const uint64_t *recv_bytes, vo
   if (!c || !recv_bytes || !dev_ptr) return KC_ERR_ARG;
   if (c->phase != PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_recv_buffer: call kc_parse first");
   CK(cudaSetDevice(c->device));
+  c->pull_ptr.clear();
   c->recv_off.assign(c->G, 0);
   c->recv_bytes.assign(recv_bytes, recv_bytes + c->G);
   uint64_t at = 0;
@@ -772,8 +777,53 @@ extern "C" int kc_exchange_recv_buffer(kc_ctx *c, const uint64_t *recv_bytes, vo
 
 extern "C" int kc_exchange_done(kc_ctx *c) {
   if (!c) return KC_ERR_ARG;
-  if (c->phase != PH_PARSED || (int)c->recv_off.size() != c->G) return fail(c, KC_ERR_STATE, "kc_exchange_done: no receive buffer");
+  if (c->phase != PH_PARSED || ((int)c->recv_off.size() != c->G && (int)c->pull_ptr.size() != c->G))
+    return fail(c, KC_ERR_STATE, "kc_exchange_done: no receive buffer and no imported regions");
   c->phase = PH_RECV_READY;
+  return KC_OK;
+}
+
+// ---- peer-memory exchange (CUDA IPC; the refine / count kernels read the peers' regions over NVLink)
+extern "C" int kc_exchange_export(kc_ctx *c, uint8_t *handle, uint64_t *region_offsets, uint64_t *region_bytes) {
+  if (!c || !handle || !region_offsets || !region_bytes) return KC_ERR_ARG;
+  if (c->phase < PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_export: call kc_parse first");
+  CK(cudaSetDevice(c->device));
+  cudaIpcMemHandle_t h;
+  CK(cudaIpcGetMemHandle(&h, c->d_bins));
+  static_assert(sizeof h == KC_IPC_HANDLE_BYTES, "IPC handle size");
+  memcpy(handle, &h, sizeof h);
+  for (int o = 0; o < c->G; o++) {
+    region_offsets[o] = c->h_region_off[o];
+    region_bytes[o] = used_region_bytes(c, o);
+  }
+  return KC_OK;
+}
+
+extern "C" int kc_exchange_import(kc_ctx *c, int src, const uint8_t *handle, uint64_t region_offset, uint64_t region_bytes) {
+  if (!c || !handle || src < 0 || src >= c->G || src == c->rank) return KC_ERR_ARG;
+  if (c->phase != PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_import: call kc_parse first");
+  CK(cudaSetDevice(c->device));
+  if ((int)c->pull_ptr.size() != c->G) {
+    c->pull_ptr.assign(c->G, nullptr);
+    c->recv_bytes.assign(c->G, 0);
+    c->recv_off.clear();
+  }
+  const std::string key(reinterpret_cast<const char *>(handle), KC_IPC_HANDLE_BYTES);
+  void *base = nullptr;
+  for (auto &m : c->ipc_mapped)
+    if (m.first == key) base = m.second;
+  if (!base) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    cudaError_t e = cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return fail(c, KC_ERR_CUDA, "kc_exchange_import: cudaIpcOpenMemHandle from rank %d: %s", src, cudaGetErrorString(e));
+    }
+    c->ipc_mapped.emplace_back(key, base);
+  }
+  c->pull_ptr[src] = region_bytes ? static_cast<uint8_t *>(base) + region_offset : nullptr;
+  c->recv_bytes[src] = region_bytes;
   return KC_OK;
 }
 
@@ -1090,6 +1140,8 @@ extern "C" int kc_insert(kc_ctx *c) {
   for (int s = 0; s < c->G; s++) {
     if (s == c->rank)
       src[s] = c->d_bins + c->h_region_off[c->rank];
+    else if ((int)c->pull_ptr.size() == c->G)
+      src[s] = c->pull_ptr[s];
     else
       src[s] = c->recv_bytes[s] ? c->d_recv + c->recv_off[s] : nullptr;
   }
@@ -1300,6 +1352,7 @@ extern "C" int kc_reset(kc_ctx *c) {
   c->phase = PH_EMPTY;
   c->caps_valid = false;  // the next kc_parse samples the reads again, as a fresh stage would
   c->recv_off.clear();
+  c->pull_ptr.clear();
   return KC_OK;
 }
 

@@ -93,6 +93,40 @@ def exchange_supermers(stage, group=None):
     return int(send_sizes.sum()), int(recv_sizes.sum()), secs
 
 
+def exchange_supermers_pull(stage, group=None):
+    """Peer-memory variant for the GPUs of one NVLink / NVSwitch node: nothing is moved here. Every rank publishes its
+    send buffer (CUDA IPC handle + per-owner region offsets / used bytes, one small all-gather), every owner maps the
+    regions meant for it, and kc_insert's refine kernel pulls the records out of the peers' HBM while it sorts them into
+    fine bins -- transfer and partition in one kernel, only used records on the links. The caller must call
+    release_peers() after finalize(), before any rank parses again. Returns (0, bytes_to_pull, 0.0)."""
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    assert world == stage.n_ranks and rank == stage.rank
+    dev = torch.device("cuda", torch.cuda.current_device())
+    stage.sync()  # this rank's bins are complete (kc_parse synchronises, this is for callers that queued more work)
+    h, off, nb = stage.export_regions()
+    mine = torch.from_numpy(np.concatenate([h.view(np.uint8), off.view(np.uint8), nb.view(np.uint8)])).to(dev)
+    rows = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(rows, mine, group=group)  # also the barrier "every rank has parsed"
+    pulled = 0
+    for s in range(world):
+        if s == rank:
+            continue
+        r = rows[s].cpu().numpy()
+        o = r[64:64 + 8 * world].view(np.uint64)
+        b = r[64 + 8 * world:64 + 16 * world].view(np.uint64)
+        stage.import_region(s, r[:64], int(o[rank]), int(b[rank]))
+        pulled += int(b[rank])
+    stage.exchange_done()
+    return 0, pulled, 0.0
+
+
+def release_peers(stage, group=None):
+    """Second half of the peer-memory exchange: my kernels are done with the peers' buffers, and theirs with mine."""
+    stage.sync()
+    dist.barrier(group=group)
+
+
 def global_avg_kmer_count(stats, group=None):
     """avg depth over all ranks = sum(count) / number of k-mers (kcount_cpu.cpp:586-596, reduce_all)."""
     backend = dist.get_backend(group)

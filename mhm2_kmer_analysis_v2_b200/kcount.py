@@ -150,6 +150,17 @@ class KcountStage:
         self._ck(self.L.kc_exchange_recv_offsets(self.h, off.ctypes.data))
         return (p.value or 0), off
 
+    def export_regions(self):
+        """Peer-memory exchange: (IPC handle bytes, offsets[n_ranks], used bytes[n_ranks]) of this rank's send buffer."""
+        h = np.zeros(64, np.uint8)
+        off, nb = np.zeros(self.n_ranks, np.uint64), np.zeros(self.n_ranks, np.uint64)
+        self._ck(self.L.kc_exchange_export(self.h, h.ctypes.data, off.ctypes.data, nb.ctypes.data))
+        return h, off, nb
+
+    def import_region(self, src, handle, offset, nbytes):
+        handle = np.ascontiguousarray(handle, np.uint8)
+        self._ck(self.L.kc_exchange_import(self.h, int(src), handle.ctypes.data, int(offset), int(nbytes)))
+
     def exchange_done(self):
         self._ck(self.L.kc_exchange_done(self.h))
 
