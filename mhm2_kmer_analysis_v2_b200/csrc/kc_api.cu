@@ -202,10 +202,12 @@ static void configure_bins(kc_ctx *c) {
   }
   // P so far is the number of FINE bins the count kernel wants. Beyond 64 K of them the parse routes by coarse bin
   // (16 fine bins each) and kc_refine.cu does the second level.
+  // With G owners the parse routes into G x P coarse bins, so the refine factor grows with G (16, 32, 64) to keep
+  // that product -- what the parse kernel's scattered writes and the capacity sample pay for -- where it is at G = 1.
   uint32_t fine_shift = 0;
   if (c->resident && P >= 65536u) {
-    fine_shift = 4;
-    P = (P + 15u) >> 4;
+    fine_shift = c->G >= 4 ? 6 : (c->G >= 2 ? 5 : 4);
+    P = (P + (1u << fine_shift) - 1u) >> fine_shift;
   }
   while ((uint64_t)P * c->G > (1u << 25)) P /= 2;
   c->fine_shift = fine_shift;
@@ -620,7 +622,8 @@ static int estimate_caps(kc_ctx *c) {
   if (n > 1) {
     const double avg_len = c->n_reads ? (double)c->n_bases / (double)c->n_reads : 0.0;
     const double per_read = std::max(1.0, 2.0 * std::max(avg_len - c->k - 1, 0.0) / (double)(c->k - c->m + 2) + 1.0);
-    want_reads = std::max<uint64_t>(want_reads, (uint64_t)(64.0 * n / per_read));
+    const double per_bin = n > 400000u ? std::max(24.0, 64.0 * 400000.0 / (double)n) : 64.0;
+    want_reads = std::max<uint64_t>(want_reads, (uint64_t)(per_bin * n / per_read));
   }
   // Which reads to look at: every stride-th read of all chunks -- or, when the input arrives in several chunks (a host
   // source is copied in sub-chunks), of the FIRST chunk only, so that the parse can start while the rest is still in
@@ -957,7 +960,7 @@ static int refine_bins(kc_ctx *c) {
     c->fine_alloc = need + need / 16;
   }
   rp.dst = c->d_fine;
-  CK(launch_refine(rp, c->sm_count, c->stream, &c->launches));
+  CK(launch_refine(rp, total / std::max<uint64_t>(rp.n_coarse, 1), c->sm_count, c->stream, &c->launches));
   uint8_t *fine = c->d_fine;
   CK(cudaMemcpyAsync(c->d_count_src + kCountMaxSrc, &fine, sizeof fine, cudaMemcpyHostToDevice, c->stream));
   CK(cudaStreamSynchronize(c->stream));  // `fine` is a local

@@ -209,7 +209,7 @@ struct RefineParams {
   unsigned int *err_too_large;
 };
 cudaError_t launch_refine_totals(const RefineParams &p, cudaStream_t s, uint64_t *launches);
-cudaError_t launch_refine(const RefineParams &p, int sm_count, cudaStream_t s, uint64_t *launches);
+cudaError_t launch_refine(const RefineParams &p, uint64_t avg_records, int sm_count, cudaStream_t s, uint64_t *launches);
 
 static const int kHeaderAlign = 64;
 

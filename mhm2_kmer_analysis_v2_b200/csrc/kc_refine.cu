@@ -17,9 +17,12 @@
 
 namespace kc {
 
-static const int RF_THREADS = 512;
 static const int RF_MAX_SUB = 256;
-static const int RF_STAGE_BYTES = 96 * 1024;  // records of a coarse bin held in shared memory (larger bins are re-read from L2)
+// Two launch shapes: coarse bins up to 96 KB are staged by 512-thread CTAs, two per SM; when the coarse bins are larger
+// (more owners -> more fine bins per coarse bin, see configure_bins) one 1024-thread CTA per SM stages up to 208 KB.
+// A coarse bin that does not fit is read twice (histogram pass, scatter pass).
+static const int RF_STAGE_SMALL = 96 * 1024, RF_THREADS_SMALL = 512;
+static const int RF_STAGE_LARGE = 208 * 1024, RF_THREADS_LARGE = 1024;
 
 // ---- step A: records per coarse bin over all sources, and their exclusive prefix
 __global__ void refine_totals_kernel(RefineParams p) {
@@ -85,7 +88,7 @@ __global__ void __launch_bounds__(1024) refine_scan_kernel(RefineParams p) {
 }
 
 // ---- step B
-template <int R>
+template <int R, int RF_THREADS, int RF_STAGE_BYTES>
 __global__ void __launch_bounds__(RF_THREADS) refine_kernel(RefineParams p) {
   constexpr int W = R / 4;
   constexpr int U = R / 16;
@@ -220,22 +223,30 @@ cudaError_t launch_refine_totals(const RefineParams &p, cudaStream_t s, uint64_t
 }
 
 template <int R>
-static cudaError_t launch_refine_r(const RefineParams &p, int grid, cudaStream_t s) {
-  cudaError_t e = cudaFuncSetAttribute(refine_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_STAGE_BYTES);
-  if (e != cudaSuccess) return e;
-  refine_kernel<R><<<grid, RF_THREADS, RF_STAGE_BYTES, s>>>(p);
+static cudaError_t launch_refine_r(const RefineParams &p, int sm_count, bool large, cudaStream_t s) {
+  uint64_t grid = (uint64_t)sm_count * (large ? 1 : 2);
+  if (grid > p.n_coarse) grid = p.n_coarse ? p.n_coarse : 1;
+  if (large) {
+    cudaError_t e = cudaFuncSetAttribute(refine_kernel<R, RF_THREADS_LARGE, RF_STAGE_LARGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_STAGE_LARGE);
+    if (e != cudaSuccess) return e;
+    refine_kernel<R, RF_THREADS_LARGE, RF_STAGE_LARGE><<<(int)grid, RF_THREADS_LARGE, RF_STAGE_LARGE, s>>>(p);
+  } else {
+    cudaError_t e = cudaFuncSetAttribute(refine_kernel<R, RF_THREADS_SMALL, RF_STAGE_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_STAGE_SMALL);
+    if (e != cudaSuccess) return e;
+    refine_kernel<R, RF_THREADS_SMALL, RF_STAGE_SMALL><<<(int)grid, RF_THREADS_SMALL, RF_STAGE_SMALL, s>>>(p);
+  }
   return cudaGetLastError();
 }
 
-cudaError_t launch_refine(const RefineParams &p, int sm_count, cudaStream_t s, uint64_t *launches) {
+// avg_records: records per coarse bin (all sources), picks the launch shape
+cudaError_t launch_refine(const RefineParams &p, uint64_t avg_records, int sm_count, cudaStream_t s, uint64_t *launches) {
   if (p.n_src > kCountMaxSrc || (1u << p.fine_shift) > (uint32_t)RF_MAX_SUB) return cudaErrorInvalidValue;
-  uint64_t grid = (uint64_t)sm_count * 2;
-  if (grid > p.n_coarse) grid = p.n_coarse ? p.n_coarse : 1;
+  const bool large = avg_records * (uint64_t)p.rec_bytes * 3 / 2 > (uint64_t)RF_STAGE_SMALL;
   (*launches)++;
   switch (p.rec_bytes) {
-    case 16: return launch_refine_r<16>(p, (int)grid, s);
-    case 32: return launch_refine_r<32>(p, (int)grid, s);
-    case 64: return launch_refine_r<64>(p, (int)grid, s);
+    case 16: return launch_refine_r<16>(p, sm_count, large, s);
+    case 32: return launch_refine_r<32>(p, sm_count, large, s);
+    case 64: return launch_refine_r<64>(p, sm_count, large, s);
   }
   return cudaErrorInvalidValue;
 }
