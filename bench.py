@@ -337,6 +337,14 @@ def main():
     inserted = stats["inserted_kmers"]  # k-mers this rank's insert launch processed
     peak, peak_src = load_peaks()
     achieved = b_alg(k) * inserted / (ms_insert_kernel / 1e3) / 1e9
+    traffic = None  # DRAM bytes of one count launch, from the committed ncu --set full capture (per k-mer, scaled)
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            tj = json.load(f)
+        if k == K_DEFAULT and not args.global_table and not args.filter:
+            traffic = tj["dram_bytes_per_counted_kmer"] * inserted
+    except Exception:
+        pass
     final_local = stats["final_kmers"]
     checksum_all = None
     if dist is not None:  # order-independent result checksum, summed over the owners (mod 2^64): the same for any exchange mode
@@ -416,7 +424,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic", "config": config_dict(args, world),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                          "kernel": "insert_kernel (HBM table)" if (args.filter or args.global_table) else "count_kernel (bin-resident insert + purge + extension resolution)",
                          "peak_source": peak_src, "b_alg_bytes_per_kmer": b_alg(k),
                          "kmers_per_launch": inserted, "ms_per_launch": ms_insert_kernel},
