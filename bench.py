@@ -403,7 +403,7 @@ def main():
         st.set_result_sink(None)
         e2e = {"value": occ_all * args.e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": int(sum_over_ranks(float(h2d_bytes))),
                "d2h_bytes_per_step": int(sum_over_ranks(float(d2h_bytes))), "steps": args.e2e_steps, "ms_per_step": dt / args.e2e_steps * 1e3,
-               "api": "kc_set_result_sink(host pinned) + kc_add_reads(host pinned) -> kc_parse [-> NCCL all-to-all] -> kc_insert -> kc_finalize (survivors land in the sink)"}
+               "api": "kc_set_result_sink(host pinned) + kc_add_reads(host pinned) -> kc_parse [-> peer-memory pull or NCCL all-to-all] -> kc_insert -> kc_finalize (survivors land in the sink)"}
 
     red = None
     if dist is not None:
