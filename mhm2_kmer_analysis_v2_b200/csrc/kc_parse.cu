@@ -21,7 +21,7 @@
 
 namespace kc {
 
-static const int SEG = 256;                            // bases of a read handled per lane and pass
+static const int SEG = 160;                            // bases of a read handled per lane and pass
 static const int NW = (SEG + 16 + 160) / 16 + 2;       // packed base words per lane (16 bases each) incl. lead + read-ahead
 static const int NQ = (SEG + 16 + 160) / 32 + 2;       // quality-bit words per lane
 static const int QCAP = 64;                            // queue entries per warp
