@@ -133,3 +133,14 @@ def test_chunked_input_copies(oracle_mod, monkeypatch, order):
     assert stats["inserted_kmers"] == reads.counted_kmers(k)
     assert_same(st.result(True), o.result(True), f"chunked input, {order}")
     st.close()
+
+
+@pytest.mark.parametrize("k,read_len", [(21, 400), (33, 251), (77, 600)])
+def test_long_reads_span_several_segments(oracle_mod, k, read_len):
+    """Reads longer than the parse kernel's 160-base segment are walked in several passes per lane."""
+    reads = K.generate(None, 3_000, seed=900 + k, read_len=read_len, **SMALL)
+    o = oracle_run(oracle_mod, reads, k)
+    st, stats = gpu_single(reads, k)
+    assert stats["inserted_kmers"] == reads.counted_kmers(k)
+    assert_same(st.result(True), o.result(True), f"k={k} read_len={read_len}")
+    st.close()
