@@ -277,6 +277,12 @@ class KmerDHT {
     Kmer<MAX_K> kmer(size_t i) const { return Kmer<MAX_K>(&keys[i * Kmer<MAX_K>::N_LONGS]); }
     KmerCounts counts_of(size_t i) const { return KmerCounts{nullptr, counts[i], left[i], right[i]}; }
   };
+  // Caller-owned host arrays that receive the survivors WHILE the count kernel runs (kc_set_result_sink): the hand-off
+  // done_all_inserts() does with a copy at the end (src/kcount/kcount-gpu/gpu_hash_table.cpp:737-785). Call before the
+  // reads are analysed; get_local_num_kmers() entries are valid afterwards (unsorted).
+  void set_result_sink(uint64_t *keys, uint16_t *counts, char *left, char *right, uint64_t capacity) {
+    ck(kc_set_result_sink(ctx, keys, counts, left, right, capacity));
+  }
   LocalKmers local_kmers(bool sorted = false) {
     LocalKmers r;
     uint64_t n = get_local_num_kmers();
