@@ -212,6 +212,7 @@ def main():
     ap.add_argument("--cpu-sample-reads", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-lookup", action="store_true", help="skip the batched-lookup measurement against the finished result")
     ap.add_argument("--exchange", default="pull", choices=["pull", "nccl"],
                     help="multi-GPU: 'pull' = peers' bins mapped with CUDA IPC, the refine kernel reads them over NVLink; "
                          "'nccl' = all-to-all of the owner regions, then refine")
@@ -353,6 +354,36 @@ def main():
         dist.all_gather_object(parts, int(cs))
         checksum_all = sum(parts) % (1 << 64)
 
+    # ---- batched lookups against the device-resident result (what the next stage asks the table)
+    lookup = None
+    if not args.no_lookup and final_local > 0:
+        rd = st.result_device(False)
+        nq = int(min(final_local, 1 << 26))
+        gen = torch.Generator(device=rd["keys"].device)
+        gen.manual_seed(4242)
+        idx = torch.randint(0, final_local, (nq,), device=rd["keys"].device, generator=gen)
+        q = rd["keys"][idx].contiguous()
+        flip = 1 << (63 - 2 * ((k - 1) % 32))
+        flip = flip - (1 << 64) if flip >= (1 << 63) else flip
+        q[1::2, st.N - 1] ^= flip  # every second query: last base changed -> (almost always) absent
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        lc, ll, lr = st.lookup_device(q)  # first call: builds the index
+        t_first = time.perf_counter() - t0
+        reps = 5
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            lc, ll, lr = st.lookup_device(q)
+        t_q = (time.perf_counter() - t0) / reps
+        hits_ok = bool(torch.equal(lc[0::2], rd["counts"][idx[0::2]]) and torch.equal(ll[0::2], rd["left"][idx[0::2]])
+                       and torch.equal(lr[0::2], rd["right"][idx[0::2]]))
+        if not hits_ok:
+            raise SystemExit("bench: lookup of the result's own keys returned something else")
+        lookup = {"queries": nq, "queries_per_sec": nq / t_q, "ms_per_batch": t_q * 1e3, "index_build_ms": max(t_first - t_q, 0.0) * 1e3,
+                  "entries": int(final_local), "hit_fraction_asked": 0.5, "miss_found": int((lc[1::2] != 0).sum().item()),
+                  "where": "queries and answers resident in HBM (kc_lookup with device pointers)"}
+        del q, idx, lc, ll, lr, rd
+
     # ---- end-to-end arm: host reads in, host result out, through the C ABI
     e2e = None
     if not args.no_e2e:
@@ -434,7 +465,7 @@ def main():
                       "table_bytes": int(g["table_bytes"]), "supermer_bytes": int(g["supermer_bytes_out"]),
                       "local_bins": int(stats["local_bins"]), "split_passes": int(stats["split_passes"]),
                       "result_bytes": int(stats["result_bytes"])},
-            "read_gen_s": t_gen,
+            "read_gen_s": t_gen, "lookup": lookup,
         }
         if world > 1:
             xs = phase["exchange_s"] / args.steps

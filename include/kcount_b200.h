@@ -209,7 +209,12 @@ int kc_result_checksum(kc_ctx *ctx, int extended, uint64_t *checksum);
 /* Text dump, one "KMER count L R" line per survivor, sorted by key (kmer_dht.cpp:274-297 writes the same
  * lines unsorted and gzipped). extended adds the 8 counters. */
 int kc_dump_sorted(kc_ctx *ctx, const char *path, int extended);
-/* Batched lookup in the finalized result: keys[n*N] HOST canonical k-mers -> counts (0 = absent), L, R. */
+/* Batched lookup in the finalized result (replaces the point lookups KmerDHT::get_local_kmer_counts / kmer_exists /
+ * get_kmer_count, src/kcount/kmer_dht.cpp:199-245, and the host map they search, kcount_gpu.cpp:439-471):
+ * keys[n*N] canonical k-mers -> counts (0 = absent: purged, dropped as X / F, or never seen), L, R (0 when absent).
+ * The first call after kc_finalize builds a device-resident index over the result; every call runs one query kernel.
+ * keys and the outputs are either all HOST pointers (staged through HBM in pieces) or all DEVICE pointers (queried in
+ * place); outputs may be NULL. Works on the unsorted result; kc_result_sort invalidates the index. */
 int kc_lookup(kc_ctx *ctx, const uint64_t *keys, uint64_t n, uint16_t *counts, char *left, char *right);
 /* Owner rank of a canonical k-mer (key_words[N]) under this context's m and n_ranks. Host-side, no GPU. */
 int kc_owner_of(const kc_ctx *ctx, const uint64_t *key_words);

@@ -35,6 +35,10 @@ struct ResultSet {
   char *left = nullptr, *right = nullptr;
   uint64_t n = 0, cap = 0;
   bool sorted = false;
+  // lookup index over the entries (kc_lookup.cu), built by the first kc_lookup after a finalize
+  unsigned long long *index = nullptr;
+  uint64_t index_slots = 0;
+  bool indexed = false;
 };
 
 static const int kSinkSlices = 12;
@@ -334,8 +338,10 @@ static void free_results(ResultSet &r) {
   dev_free(r.ext8);
   dev_free(r.left);
   dev_free(r.right);
+  dev_free(r.index);
+  r.index_slots = 0;
   r.n = r.cap = 0;
-  r.sorted = false;
+  r.sorted = r.indexed = false;
 }
 
 static void free_chunk(ReadChunk &ch) {
@@ -1074,6 +1080,7 @@ static int insert_resident(kc_ctx *c, const std::vector<uint8_t *> &src) {
   c->phase = PH_INSERTED;
   c->res_final.n = c->res_ext.n = 0;
   c->res_final.sorted = c->res_ext.sorted = false;
+  c->res_final.indexed = c->res_ext.indexed = false;
   return KC_OK;
 }
 
@@ -1203,6 +1210,7 @@ extern "C" int kc_insert(kc_ctx *c) {
   c->phase = PH_INSERTED;
   c->res_final.n = c->res_ext.n = 0;
   c->res_final.sorted = c->res_ext.sorted = false;
+  c->res_final.indexed = c->res_ext.indexed = false;
   return KC_OK;
 }
 
@@ -1210,7 +1218,7 @@ extern "C" int kc_insert(kc_ctx *c) {
 // result arrays are pooled: they only grow (the bench loop and iterative-k callers reuse them)
 static int alloc_results(kc_ctx *c, ResultSet &r, uint64_t cap, bool with_ext) {
   r.n = 0;
-  r.sorted = false;
+  r.sorted = r.indexed = false;
   if (cap <= r.cap && r.keys && (!with_ext || r.ext8)) return KC_OK;
   free_results(r);
   r.cap = cap + cap / 16 + 16;
@@ -1453,6 +1461,7 @@ extern "C" int kc_result_sort(kc_ctx *c, int extended) {
   if (!s.ext8.empty()) CK(cudaMemcpyAsync(r->ext8, s.ext8.data(), r->n * 16, cudaMemcpyHostToDevice, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   r->sorted = true;
+  r->indexed = false;  // the entries moved
   return KC_OK;
 }
 
@@ -1529,28 +1538,100 @@ extern "C" int kc_dump_sorted(kc_ctx *c, const char *path, int extended) {
   return KC_OK;
 }
 
-// host-side binary search in the sorted final result; see DESIGN.md "next" for the device-resident index
+// KmerDHT::get_local_kmer_counts / kmer_exists / get_kmer_count (src/kcount/kmer_dht.cpp:199-245) as one batched call:
+// the first lookup after a finalize builds the device index over the result (kc_lookup.cu), every call then runs one
+// query kernel. keys / outputs may be host or device pointers (all of one kind); host batches are staged through HBM.
+static int ensure_index(kc_ctx *c, ResultSet *r) {
+  if (r->indexed) return KC_OK;
+  if (r->n >= 0xffffffffULL) return fail(c, KC_ERR_STATE, "kc_lookup: more than 2^32 - 1 entries per GPU are not indexed");
+  uint64_t slots = 1024;
+  while (slots < 2 * r->n) slots <<= 1;
+  if (slots > r->index_slots) {
+    dev_free(r->index);
+    r->index_slots = 0;
+    CK(dev_alloc(&r->index, slots));
+    r->index_slots = slots;
+  }
+  IndexParams ip;
+  ip.keys = r->keys;
+  ip.counts = r->counts;
+  ip.left = r->left;
+  ip.right = r->right;
+  ip.n = r->n;
+  ip.n_words = c->N;
+  ip.slots = r->index;
+  ip.mask = slots - 1;
+  ip.err = &c->d_ctr->err_index;
+  CK(launch_index_build(ip, c->sm_count, c->stream, &c->launches));
+  unsigned int err = 0;
+  CK(cudaMemcpyAsync(&err, &c->d_ctr->err_index, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if (err) return fail(c, KC_ERR_STATE, "kc_lookup: index build did not terminate");
+  r->indexed = true;
+  return KC_OK;
+}
+
+static bool on_device(const void *p) {
+  cudaPointerAttributes at;
+  if (!p) return false;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
 extern "C" int kc_lookup(kc_ctx *c, const uint64_t *keys, uint64_t n, uint16_t *counts, char *left, char *right) {
   ResultSet *r = pick(c, 0);
   if (!r || (n && !keys)) return fail(c, KC_ERR_STATE, "kc_lookup: no result");
-  int rc = kc_result_sort(c, 0);
+  if (n == 0) return KC_OK;
+  CK(cudaSetDevice(c->device));
+  int rc = ensure_index(c, r);
   if (rc) return rc;
-  HostResult h;
-  rc = fetch(c, r, h, false);
-  if (rc) return rc;
-  const int N = c->N;
-  for (uint64_t i = 0; i < n; i++) {
-    const uint64_t *q = keys + i * N;
-    uint64_t lo = 0, hi = r->n;
-    while (lo < hi) {
-      uint64_t mid = (lo + hi) / 2;
-      if (std::lexicographical_compare(&h.keys[mid * N], &h.keys[mid * N] + N, q, q + N)) lo = mid + 1; else hi = mid;
-    }
-    bool hit = lo < r->n && std::equal(q, q + N, &h.keys[lo * N]);
-    if (counts) counts[i] = hit ? h.counts[lo] : 0;
-    if (left) left[i] = hit ? h.left[lo] : 0;
-    if (right) right[i] = hit ? h.right[lo] : 0;
+  IndexParams ip;
+  ip.keys = r->keys;
+  ip.counts = r->counts;
+  ip.left = r->left;
+  ip.right = r->right;
+  ip.n = r->n;
+  ip.n_words = c->N;
+  ip.slots = r->index;
+  {  // the allocation may be pooled from a larger result: the mask is the one the index was built with
+    uint64_t slots = 1024;
+    while (slots < 2 * r->n) slots <<= 1;
+    ip.mask = slots - 1;
   }
+  ip.err = &c->d_ctr->err_index;
+  const bool dev = on_device(keys);
+  if (dev) {
+    if ((counts && !on_device(counts)) || (left && !on_device(left)) || (right && !on_device(right)))
+      return fail(c, KC_ERR_ARG, "kc_lookup: device keys need device outputs");
+    CK(launch_index_lookup(ip, keys, n, counts, left, right, c->sm_count, c->stream, &c->launches));
+    CK(cudaStreamSynchronize(c->stream));
+    return KC_OK;
+  }
+  // host batch: staged in pieces so that an arbitrarily large batch needs a bounded amount of HBM
+  const uint64_t piece = std::min<uint64_t>(n, (uint64_t)1 << 24);
+  uint64_t *d_q = nullptr;
+  uint16_t *d_c = nullptr;
+  char *d_l = nullptr, *d_r = nullptr;
+  cudaError_t e = cudaSuccess;
+  if ((e = cudaMalloc(&d_q, piece * c->N * 8)) != cudaSuccess || (e = cudaMalloc(&d_c, piece * 2)) != cudaSuccess ||
+      (e = cudaMalloc(&d_l, piece)) != cudaSuccess || (e = cudaMalloc(&d_r, piece)) != cudaSuccess) {
+    cudaFree(d_q), cudaFree(d_c), cudaFree(d_l), cudaFree(d_r);
+    return fail(c, KC_ERR_CUDA, "kc_lookup: %s", cudaGetErrorString(e));
+  }
+  for (uint64_t q0 = 0; q0 < n && e == cudaSuccess; q0 += piece) {
+    const uint64_t nq = std::min(piece, n - q0);
+    e = cudaMemcpyAsync(d_q, keys + q0 * c->N, nq * c->N * 8, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = launch_index_lookup(ip, d_q, nq, d_c, d_l, d_r, c->sm_count, c->stream, &c->launches);
+    if (e == cudaSuccess && counts) e = cudaMemcpyAsync(counts + q0, d_c, nq * 2, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess && left) e = cudaMemcpyAsync(left + q0, d_l, nq, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess && right) e = cudaMemcpyAsync(right + q0, d_r, nq, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  }
+  cudaFree(d_q), cudaFree(d_c), cudaFree(d_l), cudaFree(d_r);
+  if (e != cudaSuccess) return fail(c, KC_ERR_CUDA, "kc_lookup: %s", cudaGetErrorString(e));
   return KC_OK;
 }
 

@@ -61,6 +61,7 @@ struct DevCounters {  // device-resident, zeroed by kc_reset
   unsigned int err_table_full, err_heavy_full;
   unsigned int err_result_full;     // bin-resident counting: the dense result arrays were too small (n_final / n_ext hold the need)
   unsigned int err_count_stack;     // bin-resident counting: a bin could not be split far enough
+  unsigned int err_index;           // lookup index: an insert did not terminate
   unsigned long long split_passes;  // extra passes over bins whose distinct k-mers did not fit shared memory
   unsigned long long parse_counted, parse_records, parse_raw;
   unsigned int err_bins_full;
@@ -210,6 +211,21 @@ struct RefineParams {
 };
 cudaError_t launch_refine_totals(const RefineParams &p, cudaStream_t s, uint64_t *launches);
 cudaError_t launch_refine(const RefineParams &p, uint64_t avg_records, int sm_count, cudaStream_t s, uint64_t *launches);
+
+// ---- lookup index over the finalized result (kc_lookup.cu)
+struct IndexParams {
+  const uint64_t *keys;  // [n * n_words] result entries
+  const uint16_t *counts;
+  const char *left, *right;
+  uint64_t n;
+  int n_words;
+  unsigned long long *slots;  // [mask + 1] fingerprint << 32 | entry, all-ones = empty
+  uint64_t mask;
+  unsigned int *err;
+};
+cudaError_t launch_index_build(const IndexParams &p, int sm_count, cudaStream_t s, uint64_t *launches);
+cudaError_t launch_index_lookup(const IndexParams &p, const uint64_t *queries, uint64_t n_queries, uint16_t *out_counts, char *out_left,
+                                char *out_right, int sm_count, cudaStream_t s, uint64_t *launches);
 
 static const int kHeaderAlign = 64;
 

@@ -182,6 +182,28 @@ class KcountStage:
                                        right.ctypes.data, ext8.ctypes.data if extended else None))
         return KmerResult(keys, counts, left, right, ext8)
 
+    def result_device(self, extended=False):
+        """Zero-copy torch views of the result arrays in HBM (kc_result_device_ptrs): keys int64 [n, N] (the u64 words),
+        counts int16 [n] (the u16 values), left / right uint8 [n]. Valid until the next count / reset / close."""
+        import torch
+
+        n = self.result_size(extended)
+        ptrs = [C.c_void_p() for _ in range(5)]
+        self._ck(self.L.kc_result_device_ptrs(self.h, int(extended), *[C.byref(p) for p in ptrs]))
+
+        class _View:
+            def __init__(self, ptr, shape, typestr):
+                self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 2}
+
+        dev = torch.device("cuda", torch.cuda.current_device())
+        if n == 0:
+            return dict(keys=torch.empty((0, self.N), dtype=torch.int64, device=dev), counts=torch.empty(0, dtype=torch.int16, device=dev),
+                        left=torch.empty(0, dtype=torch.uint8, device=dev), right=torch.empty(0, dtype=torch.uint8, device=dev))
+        return dict(keys=torch.as_tensor(_View(ptrs[0].value, (n, self.N), "<i8"), device=dev),
+                    counts=torch.as_tensor(_View(ptrs[1].value, (n,), "<i2"), device=dev),
+                    left=torch.as_tensor(_View(ptrs[2].value, (n,), "|u1"), device=dev),
+                    right=torch.as_tensor(_View(ptrs[3].value, (n,), "|u1"), device=dev))
+
     def checksum(self, extended=False):
         v = C.c_uint64()
         self._ck(self.L.kc_result_checksum(self.h, int(extended), C.byref(v)))
@@ -195,6 +217,20 @@ class KcountStage:
         n = len(keys)
         counts, left, right = np.zeros(n, np.uint16), np.zeros(n, "S1"), np.zeros(n, "S1")
         self._ck(self.L.kc_lookup(self.h, keys.ctypes.data, n, counts.ctypes.data, left.ctypes.data, right.ctypes.data))
+        return counts, left, right
+
+    def lookup_device(self, keys):
+        """kc_lookup on a batch that already lives in HBM: keys = int64 CUDA tensor [n, N] (the u64 words, bit for bit);
+        returns (counts int16, left uint8, right uint8) CUDA tensors; counts are the u16 values, bit for bit."""
+        import torch
+
+        assert keys.is_cuda and keys.dtype == torch.int64 and keys.is_contiguous()
+        n = keys.numel() // self.N
+        counts = torch.empty(n, dtype=torch.int16, device=keys.device)
+        left = torch.empty(n, dtype=torch.uint8, device=keys.device)
+        right = torch.empty(n, dtype=torch.uint8, device=keys.device)
+        torch.cuda.current_stream(keys.device).synchronize()  # the library queries on its own stream
+        self._ck(self.L.kc_lookup(self.h, keys.data_ptr(), n, counts.data_ptr(), left.data_ptr(), right.data_ptr()))
         return counts, left, right
 
     def owner_of(self, key_words):

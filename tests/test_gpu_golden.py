@@ -66,6 +66,44 @@ def test_lookup_and_dump(tmp_path):
     st.close()
 
 
+@pytest.mark.parametrize("name", ["synth_k21.npz", "synth_k33.npz", "synth_k77.npz", "synth_k99.npz"])
+def test_lookup_index_finds_every_survivor_and_nothing_else(name):
+    # KmerDHT::get_local_kmer_counts (kmer_dht.cpp:199-203): the entry of a surviving k-mer, nullptr otherwise
+    import torch
+
+    match = [p for p in GOLDEN if p.endswith(name)]
+    if not match:
+        pytest.skip(f"no golden file {name}")
+    d, k, dmin, reads, _ = load_golden(match[0])
+    st, _ = run_stage(reads, k, dmin)
+    keys = np.ascontiguousarray(d["d1_keys"]).reshape(len(d["d1_counts"]), -1)
+    n = len(keys)
+    # purged / dropped keys of the extended dump (count >= 2 but X / F) and perturbed keys must miss
+    rng = np.random.default_rng(7)
+    fake = keys.copy()
+    fake[:, -1] ^= np.uint64(1) << np.uint64(63 - 2 * ((k - 1) % 32))  # flip the last base
+    have = {kk.tobytes() for kk in keys}
+    fake = np.array([f for f in fake if f.tobytes() not in have], dtype=np.uint64).reshape(-1, keys.shape[1])
+    batch = np.concatenate([keys, fake])
+    perm = rng.permutation(len(batch))
+    c, l, r = st.lookup(batch[perm])
+    want_c = np.concatenate([d["d1_counts"], np.zeros(len(fake), np.uint16)])[perm]
+    want_l = np.concatenate([d["d1_left"], np.zeros(len(fake), np.uint8)])[perm]
+    want_r = np.concatenate([d["d1_right"], np.zeros(len(fake), np.uint8)])[perm]
+    assert np.array_equal(c, want_c)
+    assert np.array_equal(l.view(np.uint8), want_l) and np.array_equal(r.view(np.uint8), want_r)
+    # the same batch resident in HBM
+    t = torch.from_numpy(batch[perm].view(np.int64)).cuda()
+    tc, tl, tr = st.lookup_device(t)
+    assert np.array_equal(tc.cpu().numpy().view(np.uint16), want_c)
+    assert np.array_equal(tl.cpu().numpy(), want_l) and np.array_equal(tr.cpu().numpy(), want_r)
+    # sorting moves the entries: the index is rebuilt
+    st.result(False)
+    c2, _, _ = st.lookup(batch[perm][: min(1000, n)])
+    assert np.array_equal(c2, want_c[: min(1000, n)])
+    st.close()
+
+
 def test_reset_and_rerun_is_idempotent():
     d, k, dmin, reads, _ = load_golden([p for p in GOLDEN if p.endswith("synth_k33.npz")][0])
     st, _ = run_stage(reads, k, dmin)
