@@ -77,6 +77,10 @@ struct kc_ctx {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   cudaEvent_t ev_pk0 = nullptr, ev_pk1 = nullptr, ev_ik0 = nullptr, ev_ik1 = nullptr, ev_clr = nullptr;
+  // the parse launches of consecutive read chunks alternate between `stream` and this one, so that the CTAs of the next
+  // chunk move in while the last CTAs of the previous one run out (a persistent grid idles ~15 % of a launch otherwise)
+  cudaStream_t parse_stream2 = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   cudaEvent_t ev_user[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   std::string err;
   Phase phase = PH_EMPTY;
@@ -323,6 +327,9 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   for (auto &e2 : c->ev_user) cudaEventCreate(&e2);
   cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
   cudaStreamCreateWithFlags(&c->in_stream, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&c->parse_stream2, cudaStreamNonBlocking);
+  cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
   for (auto &e2 : c->ev_slice) cudaEventCreateWithFlags(&e2, cudaEventDisableTiming);
   cudaHostAlloc((void **)&c->h_slice_n, kSinkSlices * sizeof(unsigned long long), cudaHostAllocDefault);
   if ((e = dev_alloc(&c->d_ctr, 1)) != cudaSuccess) return bail(e, "cudaMalloc");
@@ -382,6 +389,9 @@ extern "C" void kc_destroy(kc_ctx *c) {
   free_chunk(c->spare);
   for (auto &e : c->ev_in_pool) cudaEventDestroy(e);
   if (c->in_stream) cudaStreamDestroy(c->in_stream);
+  if (c->parse_stream2) cudaStreamDestroy(c->parse_stream2);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   dev_free(c->d_bins);
   dev_free(c->d_bin_base);
   dev_free(c->d_bin_first);
@@ -673,10 +683,21 @@ static int run_parse(kc_ctx *c) {
   CK(cudaMemsetAsync(owner_used, 0, kCountMaxSrc * sizeof(unsigned long long), c->stream));
   CK(cudaMemsetAsync(&c->d_ctr->parse_counted, 0, 3 * sizeof(unsigned long long) + sizeof(unsigned int), c->stream));
   CK(cudaEventRecord(c->ev_pk0, c->stream));
+  const bool two = c->chunks.size() > 1 && c->parse_stream2;
+  if (two) {
+    CK(cudaEventRecord(c->ev_fork, c->stream));
+    CK(cudaStreamWaitEvent(c->parse_stream2, c->ev_fork, 0));
+  }
+  size_t ci = 0;
   for (auto &ch : c->chunks) {
-    if (ch.ready) CK(cudaStreamWaitEvent(c->stream, ch.ready, 0));
+    cudaStream_t ps = (two && (ci++ & 1)) ? c->parse_stream2 : c->stream;
+    if (ch.ready) CK(cudaStreamWaitEvent(ps, ch.ready, 0));
     ParseParams p = parse_params(c, ch, 1, 0);
-    CK(launch_parse(p, c->sm_count, c->stream, &c->launches));
+    CK(launch_parse(p, c->sm_count, ps, &c->launches));
+  }
+  if (two) {
+    CK(cudaEventRecord(c->ev_join, c->parse_stream2));
+    CK(cudaStreamWaitEvent(c->stream, c->ev_join, 0));
   }
   CK(cudaEventRecord(c->ev_pk1, c->stream));
   CK(launch_write_headers(c->d_hdr_ptrs, c->d_bin_first, c->d_cursor, c->d_bin_cap, c->G, c->P, owner_used, c->stream, &c->launches));

@@ -17,13 +17,14 @@
 //       quick_hash(minimizer) % n_ranks (src/kcount/kmer_dht.cpp:193-196), local bin = mulhi(mix(hash / n_ranks), bins), one
 //       cursor update per distinct bin in the batch, and the fixed-size record is cut out of the owning lane's packed
 //       words with funnel shifts and written with 128-bit stores into the per-(owner, bin) area of the send buffer.
+#include <algorithm>
 #include "kc_internal.h"
 
 namespace kc {
 
 static const int SEG = 160;                            // bases of a read handled per lane and pass
-static const int NW = (SEG + 16 + 160) / 16 + 2;       // packed base words per lane (16 bases each) incl. lead + read-ahead
-static const int NQ = (SEG + 16 + 160) / 32 + 2;       // quality-bit words per lane
+static const int NW = (SEG + 16) / 16 + 2;             // packed base words per lane (16 bases each): lead (< 16) + segment + 1 look-ahead
+static const int NQ = (SEG + 16) / 32 + 2;             // quality-bit words per lane
 static const int QCAP = 64;                            // queue entries per warp
 
 // 4 PackedRead bytes (first base in the lowest byte) -> 8 bits of 2-bit codes (first base highest) + 4 quality bits
@@ -121,6 +122,12 @@ __device__ __forceinline__ void drain(const ParseParams &p, const uint32_t *s_w,
   // One cursor update per record. (Merging the equal bins of a batch with match.any first costs 65 SM cycles per warp on
   // B200 -- more than the few atomics it saves with hundreds of thousands of bins.)
   // With few bins the batch is merged first (one atomic per distinct bin; a single bin would serialise 32 atomics).
+  // (the bin's base and capacity are requested before the cursor atomic, so that the two round trips overlap)
+  unsigned long long b_cap = 0, b_base = 0;
+  if (mine && !p.count_only) {
+    b_cap = __ldg(p.bin_cap + id);
+    b_base = __ldg(p.bin_base + id);
+  }
   unsigned long long slot0 = 0;
   uint32_t peers = 1u << lane;
   if (p.n_ids >= 4096u) {
@@ -134,9 +141,9 @@ __device__ __forceinline__ void drain(const ParseParams &p, const uint32_t *s_w,
   if (mine) {
     if (!p.count_only) {
       const unsigned long long slot = slot0 + __popc(peers & ((1u << lane) - 1u));
-      if (slot < p.bin_cap[id])
+      if (slot < b_cap)
         write_record<R>(s_w, s_q, meta & 31u, (meta >> 5) & 15u, (meta >> 9) & 255u, (meta >> 17) & 255u, p.k, sub,
-                        p.bins + p.bin_base[id] + slot * R);
+                        p.bins + b_base + slot * R);
       else
         p.ctr->err_bins_full = 1u;
     }
@@ -148,7 +155,7 @@ __device__ __forceinline__ void drain(const ParseParams &p, const uint32_t *s_w,
 }
 
 template <int R>
-__global__ void __launch_bounds__(256) parse_kernel(ParseParams p, int vh_len) {
+__global__ void __launch_bounds__(256, 3) parse_kernel(ParseParams p, int vh_len) {
   extern __shared__ __align__(16) uint8_t s_raw[];
   const uint32_t lane = lane_id();
   const int warp = threadIdx.x >> 5, n_warps_cta = blockDim.x >> 5;
@@ -201,22 +208,27 @@ __global__ void __launch_bounds__(256) parse_kernel(ParseParams p, int vh_len) {
         const int nch = nks ? (lead + nb + 15) >> 4 : 0;
         const int max_ch = __reduce_max_sync(0xffffffffu, nch);
         const uint4 *a0 = reinterpret_cast<const uint4 *>(src - lead);
-        uint32_t qacc = 0;
-        for (int c = 0; c < max_ch; c++) {
-          if (c < nch) {
-            const uint4 v = __ldg(a0 + c);
-            uint32_t c0, c1, c2, c3, h0, h1, h2, h3;
-            pack4(v.x, cut_add, c0, h0);
-            pack4(v.y, cut_add, c1, h1);
-            pack4(v.z, cut_add, c2, h2);
-            pack4(v.w, cut_add, c3, h3);
-            s_w[c * 32 + lane] = (c0 << 24) | (c1 << 16) | (c2 << 8) | c3;
-            const uint32_t h16 = (h0 << 12) | (h1 << 8) | (h2 << 4) | h3;
-            if (c & 1) {
-              s_q[(c >> 1) * 32 + lane] = qacc | h16;
-            } else {
-              qacc = h16 << 16;
-              s_q[(c >> 1) * 32 + lane] = qacc;
+        // four chunks per trip, all four loads issued before the first is used (the reads stream from DRAM: a lane
+        // that waits for every chunk in turn pays the full latency eleven times per segment)
+        for (int c = 0; c < max_ch; c += 4) {
+          uint4 v[4];
+#pragma unroll
+          for (int u = 0; u < 4; u++) v[u] = c + u < nch ? __ldg(a0 + c + u) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+          for (int u = 0; u < 4; u += 2) {
+            if (c + u < nch) {
+              uint32_t h16[2];
+#pragma unroll
+              for (int e = 0; e < 2; e++) {
+                uint32_t c0, c1, c2, c3, h0, h1, h2, h3;
+                pack4(v[u + e].x, cut_add, c0, h0);
+                pack4(v[u + e].y, cut_add, c1, h1);
+                pack4(v[u + e].z, cut_add, c2, h2);
+                pack4(v[u + e].w, cut_add, c3, h3);
+                if (c + u + e < nch) s_w[(c + u + e) * 32 + lane] = (c0 << 24) | (c1 << 16) | (c2 << 8) | c3;
+                h16[e] = (h0 << 12) | (h1 << 8) | (h2 << 4) | h3;
+              }
+              s_q[((c + u) >> 1) * 32 + lane] = (h16[0] << 16) | (c + u + 1 < nch ? h16[1] : 0u);
             }
           }
         }
@@ -245,10 +257,11 @@ __global__ void __launch_bounds__(256) parse_kernel(ParseParams p, int vh_len) {
         uint64_t fw = 0, rc = 0, pref = 0, run_val = 0;
         uint32_t cw = 0;
         int t = 0, run_start = 0, run_n = 0;
+        // (The run state is updated by selects AFTER the finished run has been queued: with the bookkeeping inside the
+        // branches the compiler carried seven live values through every path -- a third of the loop was register moves.)
         for (int i = 0; i <= max_steps; i++) {
-          bool want = false;
-          int out_start = 0, out_n = 0;
-          uint64_t out_val = 0;
+          bool kmer_here = false;  // a counted k-mer ends at this base
+          uint64_t wmax = 0;
           if (i < steps) {
             const int pos = lead + i;
             if ((pos & 15) == 0 || i == 0) cw = s_w[(pos >> 4) * 32 + lane];
@@ -261,30 +274,12 @@ __global__ void __launch_bounds__(256) parse_kernel(ParseParams p, int vh_len) {
               s_vh[t * 32 + lane] = canon;
               if (i >= k - 1) {
                 // k-mer starting at base s = i - k + 1: maximum of the last w canonical m-mers
-                uint64_t wmax = pref;
+                wmax = pref;
                 if (t != w - 1) {
                   const uint64_t suf = s_vh[(t + 1) * 32 + lane];
                   wmax = suf > pref ? suf : pref;
                 }
-                const int s = i - k + 1;
-                if (s >= 1) {  // s == 0 is the first k-mer of the read (or belongs to the previous segment)
-                  const int jr = s - 1;
-                  if (run_n == 0) {
-                    run_start = jr;
-                    run_val = wmax;
-                    run_n = 1;
-                  } else if (wmax != run_val || run_n == max_n) {
-                    want = true;
-                    out_start = run_start;
-                    out_n = run_n;
-                    out_val = run_val;
-                    run_start = jr;
-                    run_val = wmax;
-                    run_n = 1;
-                  } else {
-                    run_n++;
-                  }
-                }
+                kmer_here = i >= k;  // s == 0 is the first k-mer of the read (or belongs to the previous segment)
               }
               if (t == w - 1) {
                 // block of w m-mers complete: turn it into suffix maxima for the windows that start inside it
@@ -299,23 +294,25 @@ __global__ void __launch_bounds__(256) parse_kernel(ParseParams p, int vh_len) {
                 t++;
               }
             }
-          } else if (i == steps && run_n) {  // end of the segment: close the open run
-            want = true;
-            out_start = run_start;
-            out_n = run_n;
-            out_val = run_val;
-            run_n = 0;
           }
+          const bool open = run_n != 0;
+          const bool cut = kmer_here && open && (wmax != run_val || run_n == max_n);  // the k-mer starts another run
+          const bool closing = i == steps && open;                                     // end of the segment
+          const bool want = cut || closing;
           const uint32_t mask = __ballot_sync(0xffffffffu, want);
           if (mask) {
             if (want) {
               const uint32_t e = (q_head + q_count + __popc(mask & ((1u << lane) - 1u))) & (QCAP - 1);
-              Q.val[e] = out_val;
-              Q.meta[e] = lane | ((uint32_t)lead << 5) | ((uint32_t)out_start << 9) | ((uint32_t)out_n << 17);
+              Q.val[e] = run_val;
+              Q.meta[e] = lane | ((uint32_t)lead << 5) | ((uint32_t)run_start << 9) | ((uint32_t)run_n << 17);
             }
             q_count += __popc(mask);
             if (q_count >= 32) drain<R>(p, s_w, s_q, Q, q_head, q_count, n_records);
           }
+          const bool restart = kmer_here && (cut || !open);
+          run_n = restart ? 1 : (closing ? 0 : run_n + (int)kmer_here);
+          run_start = restart ? i - k : run_start;  // (record-relative number of the k-mer: s - 1)
+          run_val = restart ? wmax : run_val;
         }
       }
       // the packed words are overwritten by the next segment: everything queued must be written first
@@ -362,8 +359,11 @@ static ParseLaunch parse_launch_config(const ParseParams &p, int sm_count) {
 
 template <int R>
 static cudaError_t launch_parse_r(const ParseParams &p, int sm_count, cudaStream_t s) {
-  const ParseLaunch L = parse_launch_config(p, sm_count);
+  ParseLaunch L = parse_launch_config(p, sm_count);
   cudaFuncSetAttribute(parse_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem);
+  int resident = 0;  // the grid is persistent: exactly the CTAs that fit (registers may allow fewer than shared memory)
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, parse_kernel<R>, L.threads, L.smem) == cudaSuccess && resident > 0)
+    L.grid = std::min(L.grid, resident * sm_count);
   parse_kernel<R><<<L.grid, L.threads, L.smem, s>>>(p, L.vh_len);
   return cudaGetLastError();
 }
