@@ -319,8 +319,11 @@ def main():
     xbytes = xpulled = 0
     barrier()
     st.timer_mark(0)
+    step_wall = []
     for _ in range(args.steps):
+        t_s = time.perf_counter()
         stats, xb = one_pass()
+        step_wall.append((time.perf_counter() - t_s) * 1e3)  # (finalize returns the counters: every step ends synchronised)
         for name in ("parse", "parse_kernel", "insert", "insert_kernel", "table_clear", "finalize"):
             phase[name] += stats["ms_" + name]
         phase["exchange_s"] += xb[2]
@@ -465,7 +468,7 @@ def main():
                       "table_bytes": int(g["table_bytes"]), "supermer_bytes": int(g["supermer_bytes_out"]),
                       "local_bins": int(stats["local_bins"]), "split_passes": int(stats["split_passes"]),
                       "result_bytes": int(stats["result_bytes"])},
-            "read_gen_s": t_gen, "lookup": lookup,
+            "read_gen_s": t_gen, "lookup": lookup, "step_wall_ms": [round(x, 2) for x in step_wall],
         }
         if world > 1:
             xs = phase["exchange_s"] / args.steps

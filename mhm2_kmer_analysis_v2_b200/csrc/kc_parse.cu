@@ -155,7 +155,7 @@ __device__ __forceinline__ void drain(const ParseParams &p, const uint32_t *s_w,
 }
 
 template <int R>
-__global__ void __launch_bounds__(256, 3) parse_kernel(ParseParams p, int vh_len) {
+__global__ void __launch_bounds__(256, 4) parse_kernel(ParseParams p, int vh_len) {
   extern __shared__ __align__(16) uint8_t s_raw[];
   const uint32_t lane = lane_id();
   const int warp = threadIdx.x >> 5, n_warps_cta = blockDim.x >> 5;
