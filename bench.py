@@ -79,12 +79,19 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "200",
                                           "-i", str(self.dev)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
         except Exception:
             self.proc = None
+
+    def wait_first_sample(self, timeout_s=20.0):
+        """Block until nvidia-smi has printed its first line: its start-up (NVML initialisation over every GPU of the box)
+        holds driver locks for up to seconds and must not overlap the timed steps."""
+        t0 = time.perf_counter()
+        while self.proc and not self.lines and self.proc.poll() is None and time.perf_counter() - t0 < timeout_s:
+            time.sleep(0.02)
 
     def _pump(self):
         for line in self.proc.stdout:
@@ -308,10 +315,12 @@ def main():
     st.add_reads(reads)
     st.sync()
     # the clock sampler (an nvidia-smi process) starts before the warm-up: its start-up perturbs the driver for a moment,
-    # which must not fall into the timed region; it then samples every 100 ms through warm-up and timed steps
+    # which must not fall into the timed region; the run waits for its first sample, then it samples every 200 ms through warm-up and timed steps
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+        sampler.wait_first_sample()
+    barrier()
     for _ in range(args.warmup):
         stats, _ = one_pass()
     launches0 = st.stats()["kernel_launches"]
