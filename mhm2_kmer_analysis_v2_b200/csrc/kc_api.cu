@@ -1442,7 +1442,7 @@ static int fetch(kc_ctx *c, ResultSet *r, HostResult &h, bool want_ext) {
   return KC_OK;
 }
 
-// Sorting is not on the hot path (only dumps and tests need an order): permutation on the host, applied and written back.
+// Sorting is not on the hot path (only dumps and tests need an order): radix sort by key on the device (kc_sort.cu).
 extern "C" int kc_result_sort(kc_ctx *c, int extended) {
   ResultSet *r = pick(c, extended);
   if (!r) return fail(c, KC_ERR_STATE, "kc_result_sort: no result");
@@ -1451,36 +1451,7 @@ extern "C" int kc_result_sort(kc_ctx *c, int extended) {
     return KC_OK;
   }
   CK(cudaSetDevice(c->device));
-  HostResult h;
-  int rc = fetch(c, r, h, true);
-  if (rc) return rc;
-  const int N = c->N;
-  std::vector<uint64_t> order(r->n);
-  std::iota(order.begin(), order.end(), 0);
-  std::sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b) {
-    return std::lexicographical_compare(&h.keys[a * N], &h.keys[a * N] + N, &h.keys[b * N], &h.keys[b * N] + N);
-  });
-  HostResult s;
-  s.keys.resize(h.keys.size());
-  s.counts.resize(r->n);
-  s.left.resize(r->n);
-  s.right.resize(r->n);
-  s.ext8.resize(h.ext8.size());
-  for (uint64_t i = 0; i < r->n; i++) {
-    uint64_t o = order[i];
-    for (int j = 0; j < N; j++) s.keys[i * N + j] = h.keys[o * N + j];
-    s.counts[i] = h.counts[o];
-    s.left[i] = h.left[o];
-    s.right[i] = h.right[o];
-    if (!h.ext8.empty())
-      for (int f = 0; f < 8; f++) s.ext8[i * 8 + f] = h.ext8[o * 8 + f];
-  }
-  CK(cudaMemcpyAsync(r->keys, s.keys.data(), r->n * N * 8, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(r->counts, s.counts.data(), r->n * 2, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(r->left, s.left.data(), r->n, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemcpyAsync(r->right, s.right.data(), r->n, cudaMemcpyHostToDevice, c->stream));
-  if (!s.ext8.empty()) CK(cudaMemcpyAsync(r->ext8, s.ext8.data(), r->n * 16, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
+  CK(sort_result_by_key(r->keys, r->counts, r->left, r->right, extended ? r->ext8 : nullptr, r->n, c->N, c->sm_count, c->stream, &c->launches));
   r->sorted = true;
   r->indexed = false;  // the entries moved
   return KC_OK;

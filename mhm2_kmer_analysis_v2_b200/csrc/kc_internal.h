@@ -227,6 +227,10 @@ cudaError_t launch_index_build(const IndexParams &p, int sm_count, cudaStream_t 
 cudaError_t launch_index_lookup(const IndexParams &p, const uint64_t *queries, uint64_t n_queries, uint16_t *out_counts, char *out_left,
                                 char *out_right, int sm_count, cudaStream_t s, uint64_t *launches);
 
+// ---- result order (kc_sort.cu): entries sorted by key, word by word unsigned
+cudaError_t sort_result_by_key(uint64_t *keys, uint16_t *counts, char *left, char *right, uint16_t *ext8, uint64_t n, int n_words, int sm_count,
+                               cudaStream_t s, uint64_t *launches);
+
 static const int kHeaderAlign = 64;
 
 }  // namespace kc
