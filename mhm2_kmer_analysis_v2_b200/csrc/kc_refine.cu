@@ -13,6 +13,8 @@
 //           into ONE region with a fine header [{first record, n records}] -- the only source the count kernel then sees.
 // This replaces the receive side of the reference's supermer aggregation (src/kcount/kmer_dht.cpp:248-258: the RPC
 // target appends to a per-rank buffer) -- here the "append" also sorts by fine bin.
+#include <cstdlib>
+
 #include "kc_internal.h"
 
 namespace kc {
@@ -23,6 +25,9 @@ static const int RF_MAX_SUB = 256;
 // A coarse bin that does not fit is read twice (histogram pass, scatter pass).
 static const int RF_STAGE_SMALL = 96 * 1024, RF_THREADS_SMALL = 512;
 static const int RF_STAGE_LARGE = 208 * 1024, RF_THREADS_LARGE = 1024;
+// ... and when they are small (one GPU: ~28 KB), four 256-thread CTAs with a 48 KB stage each share an SM: the phases of
+// a bin (load, histogram, scan, scatter) are separated by barriers, and more independent CTAs keep the memory pipe busy.
+static const int RF_STAGE_TINY = 48 * 1024, RF_THREADS_TINY = 256;
 
 // ---- step A: records per coarse bin over all sources, and their exclusive prefix
 __global__ void refine_totals_kernel(RefineParams p) {
@@ -222,31 +227,34 @@ cudaError_t launch_refine_totals(const RefineParams &p, cudaStream_t s, uint64_t
   return cudaGetLastError();
 }
 
-template <int R>
-static cudaError_t launch_refine_r(const RefineParams &p, int sm_count, bool large, cudaStream_t s) {
-  uint64_t grid = (uint64_t)sm_count * (large ? 1 : 2);
+template <int R, int THREADS, int STAGE>
+static cudaError_t launch_refine_shape(const RefineParams &p, int sm_count, int ctas_per_sm, cudaStream_t s) {
+  uint64_t grid = (uint64_t)sm_count * ctas_per_sm;
   if (grid > p.n_coarse) grid = p.n_coarse ? p.n_coarse : 1;
-  if (large) {
-    cudaError_t e = cudaFuncSetAttribute(refine_kernel<R, RF_THREADS_LARGE, RF_STAGE_LARGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_STAGE_LARGE);
-    if (e != cudaSuccess) return e;
-    refine_kernel<R, RF_THREADS_LARGE, RF_STAGE_LARGE><<<(int)grid, RF_THREADS_LARGE, RF_STAGE_LARGE, s>>>(p);
-  } else {
-    cudaError_t e = cudaFuncSetAttribute(refine_kernel<R, RF_THREADS_SMALL, RF_STAGE_SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, RF_STAGE_SMALL);
-    if (e != cudaSuccess) return e;
-    refine_kernel<R, RF_THREADS_SMALL, RF_STAGE_SMALL><<<(int)grid, RF_THREADS_SMALL, RF_STAGE_SMALL, s>>>(p);
-  }
+  cudaError_t e = cudaFuncSetAttribute(refine_kernel<R, THREADS, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, STAGE);
+  if (e != cudaSuccess) return e;
+  refine_kernel<R, THREADS, STAGE><<<(int)grid, THREADS, STAGE, s>>>(p);
   return cudaGetLastError();
+}
+
+template <int R>
+static cudaError_t launch_refine_r(const RefineParams &p, int sm_count, int shape, cudaStream_t s) {
+  if (shape == 2) return launch_refine_shape<R, RF_THREADS_LARGE, RF_STAGE_LARGE>(p, sm_count, 1, s);
+  if (shape == 1) return launch_refine_shape<R, RF_THREADS_SMALL, RF_STAGE_SMALL>(p, sm_count, 2, s);
+  return launch_refine_shape<R, RF_THREADS_TINY, RF_STAGE_TINY>(p, sm_count, 4, s);
 }
 
 // avg_records: records per coarse bin (all sources), picks the launch shape
 cudaError_t launch_refine(const RefineParams &p, uint64_t avg_records, int sm_count, cudaStream_t s, uint64_t *launches) {
   if (p.n_src > kCountMaxSrc || (1u << p.fine_shift) > (uint32_t)RF_MAX_SUB) return cudaErrorInvalidValue;
-  const bool large = avg_records * (uint64_t)p.rec_bytes * 3 / 2 > (uint64_t)RF_STAGE_SMALL;
+  const uint64_t want = avg_records * (uint64_t)p.rec_bytes * 3 / 2;  // average bin + 50 %
+  int shape = want > (uint64_t)RF_STAGE_SMALL ? 2 : (want > (uint64_t)RF_STAGE_TINY ? 1 : 0);
+  if (const char *e = getenv("KC_REFINE_SHAPE")) shape = atoi(e);  // (experiments)
   (*launches)++;
   switch (p.rec_bytes) {
-    case 16: return launch_refine_r<16>(p, sm_count, large, s);
-    case 32: return launch_refine_r<32>(p, sm_count, large, s);
-    case 64: return launch_refine_r<64>(p, sm_count, large, s);
+    case 16: return launch_refine_r<16>(p, sm_count, shape, s);
+    case 32: return launch_refine_r<32>(p, sm_count, shape, s);
+    case 64: return launch_refine_r<64>(p, sm_count, shape, s);
   }
   return cudaErrorInvalidValue;
 }
