@@ -215,7 +215,7 @@ def main():
     ap.add_argument("--record-bytes", type=int, default=0)
     ap.add_argument("--table-slots", type=int, default=0, help="exact table size in slots (0 = the reference's sizing rule)")
     ap.add_argument("--global-table", action="store_true", help="count in one HBM table (kc_insert.cu) instead of bin-resident tables")
-    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-sample-reads", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -431,7 +431,8 @@ def main():
             return s
 
         st.set_result_sink(res_keys, res_counts, res_left, res_right)
-        e2e_pass()  # warm-up (allocations of the first pass)
+        for _ in range(max(2, min(args.warmup, 3))):  # warm-up: buffer pools and bin layout settle over the first two passes
+            e2e_pass()
         if args.phase_detail:
             e2e_pass(True)
         barrier()

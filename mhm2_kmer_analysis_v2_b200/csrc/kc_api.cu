@@ -215,6 +215,7 @@ static void configure_bins(kc_ctx *c) {
   uint32_t fine_shift = 0;
   if (c->resident && P >= 65536u) {
     fine_shift = c->G >= 4 ? 6 : (c->G >= 2 ? 5 : 4);
+    if (const char *e = getenv("KC_FINE_SHIFT")) fine_shift = (uint32_t)std::min(std::max(atoi(e), 1), 6);  // (experiments)
     P = (P + (1u << fine_shift) - 1u) >> fine_shift;
   }
   while ((uint64_t)P * c->G > (1u << 25)) P /= 2;
