@@ -437,8 +437,11 @@ def main():
             e2e_pass(True)
         barrier()
         t0 = time.perf_counter()
+        e2e_wall = []
         for _ in range(args.e2e_steps):
+            t_s = time.perf_counter()
             e2e_pass("nosync" if os.environ.get("KC_E2E_TRACE") else False)
+            e2e_wall.append(round((time.perf_counter() - t_s) * 1e3, 2))  # (the pass ends synchronised: finalize returns counters)
         barrier()
         dt = max_over_ranks(time.perf_counter() - t0)
         # the sink really holds the result: the counts add up to the stage's own statistic
@@ -446,7 +449,7 @@ def main():
         assert got == int(stats["sum_counts"]), f"result sink: counts sum {got} != {stats['sum_counts']}"
         st.set_result_sink(None)
         e2e = {"value": occ_all * args.e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": int(sum_over_ranks(float(h2d_bytes))),
-               "d2h_bytes_per_step": int(sum_over_ranks(float(d2h_bytes))), "steps": args.e2e_steps, "ms_per_step": dt / args.e2e_steps * 1e3,
+               "d2h_bytes_per_step": int(sum_over_ranks(float(d2h_bytes))), "steps": args.e2e_steps, "ms_per_step": dt / args.e2e_steps * 1e3, "step_wall_ms": e2e_wall,
                "api": "kc_set_result_sink(host pinned) + kc_add_reads(host pinned) -> kc_parse [-> peer-memory pull or NCCL all-to-all] -> kc_insert -> kc_finalize (survivors land in the sink)"}
 
     red = None

@@ -1039,9 +1039,19 @@ static int launch_count_pass(kc_ctx *c, bool stream_out = false) {
   }
   // Slices of bins: after every slice the result cursor comes back through pinned memory; as soon as the host sees it,
   // the new entries [done, n) go out on the copy stream while the count stream is already busy with the next slices.
+  // The copy-out is the longer leg (PCIe): it should start as early as possible, so the first two slices are small
+  // (1/48 and 1/24 of the bins: the copy of one is about as long as the count of the next), the rest equal.
+  auto slice_edge = [&](int i) -> uint32_t {
+    if (i <= 0) return 0u;
+    if (i >= kSinkSlices) return cp.n_bins;
+    const uint64_t head = (uint64_t)cp.n_bins / 48;  // slice 0
+    if (i == 1) return (uint32_t)head;
+    const uint64_t second = 3 * head;                // slice 1 ends here
+    return (uint32_t)(second + ((uint64_t)cp.n_bins - second) * (uint64_t)(i - 2) / (uint64_t)(kSinkSlices - 2));
+  };
   for (int i = 0; i < kSinkSlices; i++) {
-    cp.bin_begin = (uint32_t)((uint64_t)cp.n_bins * i / kSinkSlices);
-    cp.bin_end = (uint32_t)((uint64_t)cp.n_bins * (i + 1) / kSinkSlices);
+    cp.bin_begin = slice_edge(i);
+    cp.bin_end = slice_edge(i + 1);
     CK(launch_count(cp, c->N, dedup, c->sm_count, c->stream, &c->launches));
     CK(cudaMemcpyAsync(&c->h_slice_n[i], &c->d_ctr->n_final, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaEventRecord(c->ev_slice[i], c->stream));
