@@ -1,0 +1,49 @@
+/*
+ * kc_synth.h -- seeded synthetic PackedRead streams and the read-file format the oracle
+ * harness reads. Host-only C, no CUDA: built as its own libkc_synth.so so that the CPU arms of bench.py (the reference
+ * run, the oracle) can generate their input without mapping the product library libkcount_b200.so.
+ * No reference counterpart: the reference reads FASTQ (src/fastq.cpp); the byte format produced here is the
+ * reference's in-memory PackedRead encoding (src/packed_reads.cpp:99-126).
+ */
+#ifndef KC_SYNTH_H
+#define KC_SYNTH_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* status codes (the values of the like-named kc_status codes in kcount_b200.h) */
+enum { KC_SYNTH_OK = 0, KC_SYNTH_ERR_ARG = -1, KC_SYNTH_ERR_NOMEM = -3, KC_SYNTH_ERR_IO = -7 };
+
+typedef struct {
+  uint64_t seed;
+  uint32_t n_genomes;
+  uint64_t genome_len_min, genome_len_max; /* uniform */
+  double abundance_sigma;                  /* lognormal(0, sigma) coverage per genome; 0 = equal */
+  uint32_t read_len, read_len_min;         /* read_len_min == 0 -> fixed length */
+  double sub_rate;                         /* substitution probability per base */
+  double lowq_rate, lowq_rate_sub;         /* P(quality '+') on correct / substituted bases (0.02 / 0.5) */
+  double n_rate;                           /* P(base reported as N); 0 in every BASELINE config */
+  int32_t paired;                          /* 1: reads 2i,2i+1 are mates (fwd/rev) of one fragment */
+  double insert_mean, insert_sd;
+  int32_t qual_offset;
+  uint32_t reserved[5];
+} kc_synth_config;
+typedef struct kc_synth kc_synth;
+void kc_synth_config_default(kc_synth_config *cfg); /* config C1 of BASELINE.md with seed 1001 */
+int kc_synth_create(const kc_synth_config *cfg, kc_synth **out);
+void kc_synth_destroy(kc_synth *s);
+/* reads [first, first+n) of the infinite seeded stream; read i depends only on (seed, i). bytes must hold
+ * n*read_len; offsets/lens hold n entries; offsets are relative to bytes. Returns bytes used in *n_bytes. */
+int kc_synth_generate(const kc_synth *s, uint64_t first, uint64_t n, uint8_t *bytes, uint64_t *offsets, uint16_t *lens,
+                      uint64_t *n_bytes, int n_threads);
+int kc_reads_save(const char *path, const uint8_t *bytes, uint64_t n_bytes, const uint64_t *offsets, const uint16_t *lens,
+                  uint64_t n_reads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KC_SYNTH_H */

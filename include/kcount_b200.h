@@ -27,7 +27,6 @@
  *   kc_get_stats             <- HashTableGPUDriver::get_stats + the stage's reduce_one() counters
  *                                                                                   src/kcount/kcount_gpu.cpp:294-364
  *   kc_run                   <- analyze_kmers<MAX_K> (single rank)                  src/kcount/kcount.cpp:143-161
- *   kc_synth_* / kc_reads_*  <- (no reference counterpart) seeded synthetic PackedRead streams, BASELINE.md section 4
  *
  * Semantics are those of the reference's CPU build (src/kcount/kcount_cpu.cpp): N counts as G inside a
  * k-mer and never as an extension, quality only masks extension bases, the first and last k-mer of a
@@ -43,7 +42,7 @@
 extern "C" {
 #endif
 
-#define KC_ABI_VERSION 1
+#define KC_ABI_VERSION 2
 #define KC_MAX_K 127       /* 4 x u64 key words; k must not be a multiple of 32 */
 #define KC_MAX_KEY_WORDS 4
 
@@ -122,6 +121,11 @@ typedef struct {
   uint64_t local_bins;         /* sub-bins per owner actually used */
   uint64_t split_passes;       /* bin-resident mode: extra passes over bins whose distinct k-mers did not fit shared memory */
   uint64_t result_bytes;       /* device bytes of the dense result arrays */
+  /* the resident insert pipeline (refine -> count, slice by slice) */
+  double ms_refine_kernel;     /* refine kernels (second partition level), sum over the slices, on their own stream */
+  double ms_exchange_copy;     /* copy-mode exchange: first copy start to last copy end on the transfer streams */
+  uint64_t exchange_copy_bytes;/* bytes the copy engines moved from the peers in that window */
+  uint64_t pipeline_slices;    /* slices the last kc_insert was cut into */
 } kc_stats;
 
 /* ---- lifecycle ---------------------------------------------------------------------------------- */
@@ -136,7 +140,7 @@ int kc_device_count(void);
 /* Append reads. bytes: PackedRead encoding, one byte per base = base(A0 C1 G2 T3 N4) | min(q,31) << 3.
  * offsets[i] = start of read i inside `bytes`; lens[i] = its length. n_bytes = extent of `bytes`.
  * Pointers may be host (pageable or pinned) or device memory; the data is copied to the device (async
- * on the context's stream when pinned/device) and may be released after kc_sync(). */
+ * on the context's input stream when pinned/device) and may be released or overwritten after kc_sync(). */
 int kc_add_reads(kc_ctx *ctx, const uint8_t *bytes, uint64_t n_bytes, const uint64_t *offsets, const uint16_t *lens,
                  uint64_t n_reads);
 int kc_clear_reads(kc_ctx *ctx);
@@ -167,6 +171,23 @@ int kc_exchange_done(kc_ctx *ctx);
 int kc_exchange_export(kc_ctx *ctx, uint8_t *handle /* [KC_IPC_HANDLE_BYTES] */, uint64_t *region_offsets /* [n_ranks] */,
                        uint64_t *region_bytes /* [n_ranks] */);
 int kc_exchange_import(kc_ctx *ctx, int src_rank, const uint8_t *handle, uint64_t region_offset, uint64_t region_bytes);
+/* How kc_insert gets at the imported regions. KC_XCHG_PULL (default): the refine / count kernels read the peers' memory
+ * directly (transfer fused into the partition kernel). KC_XCHG_COPY: copy engines move the regions slice by slice into a
+ * local buffer on separate streams while the refine and count kernels work on the previous slices -- no SM does transfer
+ * work, and the NVLink time hides behind the count pass. For slice-granular copies the exporter's slice table travels
+ * with the handle: kc_exchange_export_slices fills offsets[n_ranks][KC_MAX_SLICES + 1] (byte offset of every slice edge
+ * inside each owner's region; entries beyond n_slices repeat the end), the importer hands row [its own rank] of source s
+ * to kc_exchange_import_slices. Without a table the whole region moves with the first slice. */
+#define KC_XCHG_PULL 0
+#define KC_XCHG_COPY 1
+#define KC_MAX_SLICES 12
+int kc_exchange_set_mode(kc_ctx *ctx, int mode);
+int kc_exchange_export_slices(kc_ctx *ctx, uint32_t *n_slices, uint64_t *offsets /* [n_ranks * (KC_MAX_SLICES + 1)] */);
+int kc_exchange_import_slices(kc_ctx *ctx, int src_rank, uint32_t n_slices, const uint64_t *offsets /* [n_slices + 1] */);
+/* After that barrier: frees send buffers this rank exported earlier and has since replaced by a larger one (they stay
+ * allocated until here because a peer may still have had them mapped; an importer closes a stale mapping when the
+ * source's next export carries a new handle). Cheap no-op otherwise. */
+int kc_exchange_release(kc_ctx *ctx);
 /* (3)+(4) insert every received supermer's k-mers into the table (through the filter when enabled). */
 int kc_insert(kc_ctx *ctx);
 /* (5) purge count<2, resolve extensions, compact survivors. Synchronises and fills stats. */
@@ -220,34 +241,11 @@ int kc_lookup(kc_ctx *ctx, const uint64_t *keys, uint64_t n, uint16_t *counts, c
 int kc_owner_of(const kc_ctx *ctx, const uint64_t *key_words);
 uint32_t kc_minimizer_len(const kc_ctx *ctx);
 
-/* ---- host helpers: pinned memory, synthetic reads, read files ------------------------------------ */
+/* ---- host helpers: pinned memory ------------------------------------------------------------------- */
 int kc_host_alloc(void **ptr, size_t bytes); /* cudaHostAlloc */
 int kc_host_free(void *ptr);
 
-typedef struct {
-  uint64_t seed;
-  uint32_t n_genomes;
-  uint64_t genome_len_min, genome_len_max; /* uniform */
-  double abundance_sigma;                  /* lognormal(0, sigma) coverage per genome; 0 = equal */
-  uint32_t read_len, read_len_min;         /* read_len_min == 0 -> fixed length */
-  double sub_rate;                         /* substitution probability per base */
-  double lowq_rate, lowq_rate_sub;         /* P(quality '+') on correct / substituted bases (0.02 / 0.5) */
-  double n_rate;                           /* P(base reported as N); 0 in every BASELINE config */
-  int32_t paired;                          /* 1: reads 2i,2i+1 are mates (fwd/rev) of one fragment */
-  double insert_mean, insert_sd;
-  int32_t qual_offset;
-  uint32_t reserved[5];
-} kc_synth_config;
-typedef struct kc_synth kc_synth;
-void kc_synth_config_default(kc_synth_config *cfg); /* config C1 of BASELINE.md with seed 1001 */
-int kc_synth_create(const kc_synth_config *cfg, kc_synth **out);
-void kc_synth_destroy(kc_synth *s);
-/* reads [first, first+n) of the infinite seeded stream; read i depends only on (seed, i). bytes must hold
- * n*read_len; offsets/lens hold n entries; offsets are relative to bytes. Returns bytes used in *n_bytes. */
-int kc_synth_generate(const kc_synth *s, uint64_t first, uint64_t n, uint8_t *bytes, uint64_t *offsets, uint16_t *lens,
-                      uint64_t *n_bytes, int n_threads);
-int kc_reads_save(const char *path, const uint8_t *bytes, uint64_t n_bytes, const uint64_t *offsets, const uint16_t *lens,
-                  uint64_t n_reads);
+/* seeded synthetic PackedRead streams and read files: include/kc_synth.h (libkc_synth.so, host-only, no CUDA) */
 
 #ifdef __cplusplus
 }

@@ -11,7 +11,8 @@ LIB_PATH = os.path.join(HERE, "libkcount_b200.so")
 
 KC_OK = 0
 KC_ERR_ARG, KC_ERR_CUDA, KC_ERR_NOMEM, KC_ERR_TABLE_FULL, KC_ERR_BINS_FULL, KC_ERR_STATE, KC_ERR_IO = -1, -2, -3, -4, -5, -6, -7
-KC_ABI_VERSION = 1
+KC_ABI_VERSION = 2
+KC_XCHG_PULL, KC_XCHG_COPY, KC_MAX_SLICES = 0, 1, 12
 KC_FLAG_KEEP_EXT_COUNTS = 1
 KC_FLAG_NO_WARP_DEDUP = 2
 KC_FLAG_GLOBAL_TABLE = 4
@@ -38,7 +39,8 @@ class KcStats(C.Structure):
         ("avg_kmer_count", C.c_double), ("ms_parse", C.c_double), ("ms_insert", C.c_double), ("ms_finalize", C.c_double),
         ("kernel_launches", C.c_uint64), ("ms_parse_kernel", C.c_double), ("ms_insert_kernel", C.c_double),
         ("ms_table_clear", C.c_double), ("insert_kernel_launches", C.c_uint64), ("local_bins", C.c_uint64),
-        ("split_passes", C.c_uint64), ("result_bytes", C.c_uint64)]
+        ("split_passes", C.c_uint64), ("result_bytes", C.c_uint64), ("ms_refine_kernel", C.c_double), ("ms_exchange_copy", C.c_double),
+        ("exchange_copy_bytes", C.c_uint64), ("pipeline_slices", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -72,6 +74,10 @@ PROTOTYPES = {
     "kc_exchange_done": (C.c_int, [vp]),
     "kc_exchange_export": (C.c_int, [vp, vp, vp, vp]),
     "kc_exchange_import": (C.c_int, [vp, C.c_int, vp, C.c_uint64, C.c_uint64]),
+    "kc_exchange_release": (C.c_int, [vp]),
+    "kc_exchange_set_mode": (C.c_int, [vp, C.c_int]),
+    "kc_exchange_export_slices": (C.c_int, [vp, C.POINTER(C.c_uint32), vp]),
+    "kc_exchange_import_slices": (C.c_int, [vp, C.c_int, C.c_uint32, vp]),
     "kc_insert": (C.c_int, [vp]),
     "kc_finalize": (C.c_int, [vp, C.POINTER(KcStats)]),
     "kc_run": (C.c_int, [vp, C.POINTER(KcStats)]),
@@ -93,14 +99,35 @@ PROTOTYPES = {
     "kc_minimizer_len": (C.c_uint32, [vp]),
     "kc_host_alloc": (C.c_int, [C.POINTER(vp), C.c_size_t]),
     "kc_host_free": (C.c_int, [vp]),
+}
+
+# every symbol include/kc_synth.h declares (libkc_synth.so: host-only C, no CUDA -- the CPU arms of bench.py load only this)
+SYNTH_PROTOTYPES = {
     "kc_synth_config_default": (None, [C.POINTER(KcSynthConfig)]),
     "kc_synth_create": (C.c_int, [C.POINTER(KcSynthConfig), C.POINTER(vp)]),
     "kc_synth_destroy": (None, [vp]),
     "kc_synth_generate": (C.c_int, [vp, C.c_uint64, C.c_uint64, vp, vp, vp, C.POINTER(C.c_uint64), C.c_int]),
     "kc_reads_save": (C.c_int, [C.c_char_p, vp, C.c_uint64, vp, vp, C.c_uint64]),
 }
+SYNTH_LIB_PATH = os.path.join(HERE, "libkc_synth.so")
 
 _lib = None
+_synth = None
+
+
+def synth_lib():
+    """libkc_synth.so: the seeded read generator and the read-file writer (include/kc_synth.h)."""
+    global _synth
+    if _synth is None:
+        if not os.path.exists(SYNTH_LIB_PATH):
+            raise ImportError(f"{SYNTH_LIB_PATH} is missing: build it with `make -C {os.path.join(HERE, 'csrc')}`")
+        L = C.CDLL(SYNTH_LIB_PATH)
+        for name, (res, args) in SYNTH_PROTOTYPES.items():
+            f = getattr(L, name)
+            f.restype = res
+            f.argtypes = args
+        _synth = L
+    return _synth
 
 
 def build():

@@ -41,7 +41,11 @@ struct ResultSet {
   bool indexed = false;
 };
 
-static const int kSinkSlices = 12;
+static const int kSinkSlices = kSlices;
+static_assert(KC_MAX_SLICES == kSlices, "the ABI's slice table and the pipeline disagree");
+static const int kXferStreams = 4;  // copy-engine streams of the copy-mode exchange (peers are dealt round-robin)
+static const int kPinnedWords = 4 * kCountMaxSrc + 64;  // pinned staging for small host <-> device parameter copies
+static const int kScratchWords = 64;                    // device scratch (checksums, small reductions)
 
 struct kc_ctx {
   kc_config cfg;
@@ -73,6 +77,27 @@ struct kc_ctx {
   ReadChunk spare;  // buffers of the last kc_clear_reads, reused by the next kc_add_reads
   cudaEvent_t ev_slice[kSinkSlices];
   unsigned long long *h_slice_n = nullptr;  // pinned: n_final after every slice
+  unsigned long long *h_pinned = nullptr;   // pinned staging [kPinnedWords]
+  unsigned long long *d_scratch = nullptr;  // [kScratchWords]
+  // refine / receive pipeline: slice i of the coarse bins is refined on refine_stream while slice i - 1 is counted
+  cudaStream_t refine_stream = nullptr;
+  cudaEvent_t ev_rs0[kSinkSlices], ev_rs1[kSinkSlices];  // refine slice i: start / end (refine_stream)
+  cudaEvent_t ev_cs0[kSinkSlices], ev_cs1[kSinkSlices];  // count slice i: start / end (stream)
+  int n_count_slices = 0, n_refine_slices = 0;
+  // copy-mode exchange (kc_exchange_set_mode(KC_XCHG_COPY)): copy engines move the peers' regions into d_recv
+  int xmode = KC_XCHG_PULL;
+  cudaStream_t xfer_stream[kXferStreams] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_x[kXferStreams], ev_xbeg[kXferStreams], ev_xend[kXferStreams];
+  bool xfer_started[kXferStreams] = {false, false, false, false};
+  uint64_t xfer_bytes = 0;
+  std::vector<uint64_t> h_slice_off;                  // [G * (kSlices + 1)] slice edges inside each owner's region of MY send buffer
+  std::vector<std::vector<uint64_t>> peer_slice_off;  // [G][n_slices + 1] the same table of every source, for my region in it
+  uint64_t last_final = 0, last_ext = 0;              // result sizes of this context's previous run (result reservation)
+  // pooled staging of kc_lookup's host batches
+  uint64_t *d_lq = nullptr;
+  uint16_t *d_lc = nullptr;
+  char *d_ll = nullptr, *d_lr = nullptr;
+  uint64_t lookup_cap = 0;
   int device = 0, sm_count = 148;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -103,7 +128,12 @@ struct kc_ctx {
 
   // receive side
   std::vector<uint8_t *> pull_ptr;                         // peer-memory exchange: region of source s in ITS memory (IPC-mapped)
-  std::vector<std::pair<std::string, void *>> ipc_mapped;  // opened IPC handles (raw bytes -> base pointer)
+  // opened IPC mappings, one per source rank (handle bytes -> base pointer). A source that re-allocated its send buffer
+  // exports a new handle: the stale mapping is closed before the new one is opened (kc_exchange_import); the exporter
+  // keeps the old allocation alive until kc_exchange_release, i.e. until every importer has let go of it.
+  std::vector<std::pair<std::string, void *>> ipc_mapped;
+  bool bins_exported = false;            // d_bins has been handed to peers since it was allocated
+  std::vector<uint8_t *> retired_bins;   // exported send buffers replaced by a larger one, freed by kc_exchange_release
   uint8_t *d_recv = nullptr;
   uint64_t recv_alloc = 0;
   std::vector<uint64_t> recv_off, recv_bytes;
@@ -128,6 +158,13 @@ struct kc_ctx {
   ResultSet res_final, res_ext;
   kc_stats stats;
   uint64_t launches = 0;
+  kc_ctx() {
+    for (auto &e : ev_slice) e = nullptr;
+    for (auto *arr : {ev_rs0, ev_rs1, ev_cs0, ev_cs1})
+      for (int i = 0; i < kSinkSlices; i++) arr[i] = nullptr;
+    for (auto *arr : {ev_x, ev_xbeg, ev_xend})
+      for (int i = 0; i < kXferStreams; i++) arr[i] = nullptr;
+  }
 };
 
 // ------------------------------------------------------------------------------------------------ helpers
@@ -317,24 +354,39 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   cudaDeviceProp prop;
   if ((e = cudaGetDeviceProperties(&prop, dev)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
   c->sm_count = prop.multiProcessorCount;
-  if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
-  cudaEventCreate(&c->ev0);
-  cudaEventCreate(&c->ev1);
-  cudaEventCreate(&c->ev_pk0);
-  cudaEventCreate(&c->ev_pk1);
-  cudaEventCreate(&c->ev_ik0);
-  cudaEventCreate(&c->ev_ik1);
-  cudaEventCreate(&c->ev_clr);
-  for (auto &e2 : c->ev_user) cudaEventCreate(&e2);
-  cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
-  cudaStreamCreateWithFlags(&c->in_stream, cudaStreamNonBlocking);
-  cudaStreamCreateWithFlags(&c->parse_stream2, cudaStreamNonBlocking);
-  cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
-  cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming);
-  for (auto &e2 : c->ev_slice) cudaEventCreateWithFlags(&e2, cudaEventDisableTiming);
-  cudaHostAlloc((void **)&c->h_slice_n, kSinkSlices * sizeof(unsigned long long), cudaHostAllocDefault);
-  if ((e = dev_alloc(&c->d_ctr, 1)) != cudaSuccess) return bail(e, "cudaMalloc");
-  cudaMemsetAsync(c->d_ctr, 0, sizeof(DevCounters), c->stream);
+  // every handle is checked: a failure here must be a kc_status now, not a null-handle crash in a later phase
+#define CREATE_CK(call)                                 \
+  do {                                                  \
+    if ((e = (call)) != cudaSuccess) {                  \
+      int code_ = fail(nullptr, e == cudaErrorMemoryAllocation ? KC_ERR_NOMEM : KC_ERR_CUDA, "kc_create: %s: %s", #call, cudaGetErrorString(e)); \
+      kc_destroy(c);                                    \
+      return code_;                                     \
+    }                                                   \
+  } while (0)
+  CREATE_CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  for (cudaEvent_t *ev : {&c->ev0, &c->ev1, &c->ev_pk0, &c->ev_pk1, &c->ev_ik0, &c->ev_ik1, &c->ev_clr}) CREATE_CK(cudaEventCreate(ev));
+  for (auto &e2 : c->ev_user) CREATE_CK(cudaEventCreate(&e2));
+  CREATE_CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  CREATE_CK(cudaStreamCreateWithFlags(&c->in_stream, cudaStreamNonBlocking));
+  CREATE_CK(cudaStreamCreateWithFlags(&c->parse_stream2, cudaStreamNonBlocking));
+  CREATE_CK(cudaStreamCreateWithFlags(&c->refine_stream, cudaStreamNonBlocking));
+  CREATE_CK(cudaEventCreate(&c->ev_fork));
+  CREATE_CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+  for (auto &e2 : c->ev_slice) CREATE_CK(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+  for (auto *arr : {c->ev_rs0, c->ev_rs1, c->ev_cs0, c->ev_cs1})
+    for (int i = 0; i < kSinkSlices; i++) CREATE_CK(cudaEventCreate(&arr[i]));
+  for (int q = 0; q < kXferStreams; q++) {
+    CREATE_CK(cudaStreamCreateWithFlags(&c->xfer_stream[q], cudaStreamNonBlocking));
+    CREATE_CK(cudaEventCreateWithFlags(&c->ev_x[q], cudaEventDisableTiming));
+    CREATE_CK(cudaEventCreate(&c->ev_xbeg[q]));
+    CREATE_CK(cudaEventCreate(&c->ev_xend[q]));
+  }
+  CREATE_CK(cudaHostAlloc((void **)&c->h_slice_n, kSinkSlices * sizeof(unsigned long long), cudaHostAllocDefault));
+  CREATE_CK(cudaHostAlloc((void **)&c->h_pinned, kPinnedWords * sizeof(unsigned long long), cudaHostAllocDefault));
+  CREATE_CK(dev_alloc(&c->d_ctr, 1));
+  CREATE_CK(dev_alloc(&c->d_scratch, kScratchWords));
+  CREATE_CK(cudaMemsetAsync(c->d_ctr, 0, sizeof(DevCounters), c->stream));
+#undef CREATE_CK
   configure_bins(c);
   *out = c;
   return KC_OK;
@@ -362,8 +414,8 @@ static void free_chunk(ReadChunk &ch) {
 extern "C" int kc_clear_reads(kc_ctx *c) {
   if (!c) return KC_ERR_ARG;
   cudaSetDevice(c->device);
-  cudaStreamSynchronize(c->in_stream);
-  cudaStreamSynchronize(c->stream);
+  if (c->in_stream) cudaStreamSynchronize(c->in_stream);
+  if (c->stream) cudaStreamSynchronize(c->stream);
   for (auto &ch : c->chunks) {
     if (!ch.owner) continue;
     // keep the largest allocation for the next kc_add_reads (cudaMalloc / cudaFree of gigabytes are not free)
@@ -386,7 +438,9 @@ extern "C" int kc_clear_reads(kc_ctx *c) {
 extern "C" void kc_destroy(kc_ctx *c) {
   if (!c) return;
   kc_clear_reads(c);
-  for (auto &m : c->ipc_mapped) cudaIpcCloseMemHandle(m.second);
+  for (auto &m : c->ipc_mapped)
+    if (m.second) cudaIpcCloseMemHandle(m.second);
+  for (auto p : c->retired_bins) cudaFree(p);
   free_chunk(c->spare);
   for (auto &e : c->ev_in_pool) cudaEventDestroy(e);
   if (c->in_stream) cudaStreamDestroy(c->in_stream);
@@ -426,7 +480,22 @@ extern "C" void kc_destroy(kc_ctx *c) {
     if (e) cudaEventDestroy(e);
   for (auto &e : c->ev_slice)
     if (e) cudaEventDestroy(e);
+  for (auto *arr : {c->ev_rs0, c->ev_rs1, c->ev_cs0, c->ev_cs1})
+    for (int i = 0; i < kSinkSlices; i++)
+      if (arr[i]) cudaEventDestroy(arr[i]);
+  for (auto *arr : {c->ev_x, c->ev_xbeg, c->ev_xend})
+    for (int i = 0; i < kXferStreams; i++)
+      if (arr[i]) cudaEventDestroy(arr[i]);
+  for (auto &xs : c->xfer_stream)
+    if (xs) cudaStreamDestroy(xs);
   if (c->h_slice_n) cudaFreeHost(c->h_slice_n);
+  if (c->h_pinned) cudaFreeHost(c->h_pinned);
+  dev_free(c->d_scratch);
+  dev_free(c->d_lq);
+  dev_free(c->d_lc);
+  dev_free(c->d_ll);
+  dev_free(c->d_lr);
+  if (c->refine_stream) cudaStreamDestroy(c->refine_stream);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
@@ -435,7 +504,9 @@ extern "C" void kc_destroy(kc_ctx *c) {
 extern "C" int kc_sync(kc_ctx *c) {
   if (!c) return KC_ERR_ARG;
   CK(cudaSetDevice(c->device));
+  CK(cudaStreamSynchronize(c->in_stream));  // the input copies of kc_add_reads: the caller may reuse its buffers after this
   CK(cudaStreamSynchronize(c->stream));
+  CK(cudaStreamSynchronize(c->refine_stream));
   CK(cudaStreamSynchronize(c->copy_stream));
   return KC_OK;
 }
@@ -602,7 +673,12 @@ static int layout_bins(kc_ctx *c, double scale) {
   }
   c->bins_bytes = h[kCountMaxSrc + c->G];
   if (c->bins_bytes > c->bins_alloc) {
+    if (c->bins_exported && c->d_bins) {
+      c->retired_bins.push_back(c->d_bins);  // peers may still hold it mapped: freed by kc_exchange_release
+      c->d_bins = nullptr;
+    }
     dev_free(c->d_bins);
+    c->bins_exported = false;
     uint64_t want = c->bins_bytes + c->bins_bytes / 16;
     CK(dev_alloc(&c->d_bins, want));
     c->bins_alloc = want;
@@ -610,6 +686,22 @@ static int layout_bins(kc_ctx *c, double scale) {
   std::vector<uint8_t *> hdr(c->G);
   for (int o = 0; o < c->G; o++) hdr[o] = c->d_bins + c->h_region_off[o];
   CK(cudaMemcpyAsync(c->d_hdr_ptrs, hdr.data(), c->G * sizeof(uint8_t *), cudaMemcpyHostToDevice, c->stream));
+  c->h_slice_off.clear();
+  if (c->G > 1) {
+    // where every pipeline slice of coarse bins starts inside each owner's region: the importers of the copy-mode
+    // exchange cut their transfers there (the layout is by capacity, so this is known before a record is written)
+    const int S = (uint32_t)c->P >= 64u * kSlices ? kSlices : 1;
+    const size_t n = (size_t)c->G * (S + 1);
+    unsigned long long *d_so = nullptr;
+    CK(dev_alloc(&d_so, n));
+    cudaError_t e = launch_slice_offsets(c->d_bin_first, c->d_bin_cap, (uint32_t)c->G, (uint32_t)c->P, S, c->header_bytes, c->rec_bytes, d_so,
+                                         c->stream, &c->launches);
+    c->h_slice_off.assign(n, 0);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(c->h_slice_off.data(), d_so, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_so);
+    CK(e);
+  }
   CK(cudaStreamSynchronize(c->stream));  // hdr is a local
   return KC_OK;
 }
@@ -760,6 +852,7 @@ extern "C" int kc_parse(kc_ctx *c) {
   c->phase = PH_PARSED;
   c->recv_off.clear();
   c->pull_ptr.clear();
+  c->peer_slice_off.clear();
   return KC_OK;
 }
 
@@ -810,6 +903,23 @@ extern "C" int kc_exchange_done(kc_ctx *c) {
   if (!c) return KC_ERR_ARG;
   if (c->phase != PH_PARSED || ((int)c->recv_off.size() != c->G && (int)c->pull_ptr.size() != c->G))
     return fail(c, KC_ERR_STATE, "kc_exchange_done: no receive buffer and no imported regions");
+  if ((int)c->pull_ptr.size() == c->G && c->xmode == KC_XCHG_COPY) {
+    // copy mode: the imported regions land in d_recv (same layout as the all-to-all's receive buffer)
+    CK(cudaSetDevice(c->device));
+    c->recv_off.assign(c->G, 0);
+    uint64_t at = 0;
+    for (int s = 0; s < c->G; s++) {
+      c->recv_off[s] = at;
+      if (s != c->rank) at += (c->recv_bytes[s] + 255) & ~255ULL;
+    }
+    if (at > c->recv_alloc) {
+      CK(cudaStreamSynchronize(c->stream));
+      dev_free(c->d_recv);
+      c->recv_alloc = 0;
+      CK(dev_alloc(&c->d_recv, at + at / 16 + 256));
+      c->recv_alloc = at + at / 16 + 256;
+    }
+  }
   c->phase = PH_RECV_READY;
   return KC_OK;
 }
@@ -823,10 +933,19 @@ extern "C" int kc_exchange_export(kc_ctx *c, uint8_t *handle, uint64_t *region_o
   CK(cudaIpcGetMemHandle(&h, c->d_bins));
   static_assert(sizeof h == KC_IPC_HANDLE_BYTES, "IPC handle size");
   memcpy(handle, &h, sizeof h);
+  c->bins_exported = true;
   for (int o = 0; o < c->G; o++) {
     region_offsets[o] = c->h_region_off[o];
     region_bytes[o] = used_region_bytes(c, o);
   }
+  return KC_OK;
+}
+
+extern "C" int kc_exchange_release(kc_ctx *c) {
+  if (!c) return KC_ERR_ARG;
+  CK(cudaSetDevice(c->device));
+  for (auto p : c->retired_bins) cudaFree(p);
+  c->retired_bins.clear();
   return KC_OK;
 }
 
@@ -838,11 +957,16 @@ extern "C" int kc_exchange_import(kc_ctx *c, int src, const uint8_t *handle, uin
     c->pull_ptr.assign(c->G, nullptr);
     c->recv_bytes.assign(c->G, 0);
     c->recv_off.clear();
+    c->peer_slice_off.clear();
   }
   const std::string key(reinterpret_cast<const char *>(handle), KC_IPC_HANDLE_BYTES);
-  void *base = nullptr;
-  for (auto &m : c->ipc_mapped)
-    if (m.first == key) base = m.second;
+  if ((int)c->ipc_mapped.size() != c->G) c->ipc_mapped.assign(c->G, std::make_pair(std::string(), (void *)nullptr));
+  auto &slot = c->ipc_mapped[src];
+  if (slot.second && slot.first != key) {  // the source re-allocated its send buffer: let go of the old one
+    cudaIpcCloseMemHandle(slot.second);
+    slot.second = nullptr;
+  }
+  void *base = slot.second;
   if (!base) {
     cudaIpcMemHandle_t h;
     memcpy(&h, handle, sizeof h);
@@ -851,10 +975,40 @@ extern "C" int kc_exchange_import(kc_ctx *c, int src, const uint8_t *handle, uin
       cudaGetLastError();
       return fail(c, KC_ERR_CUDA, "kc_exchange_import: cudaIpcOpenMemHandle from rank %d: %s", src, cudaGetErrorString(e));
     }
-    c->ipc_mapped.emplace_back(key, base);
+    slot.first = key;
+    slot.second = base;
   }
   c->pull_ptr[src] = region_bytes ? static_cast<uint8_t *>(base) + region_offset : nullptr;
   c->recv_bytes[src] = region_bytes;
+  return KC_OK;
+}
+
+extern "C" int kc_exchange_set_mode(kc_ctx *c, int mode) {
+  if (!c || (mode != KC_XCHG_PULL && mode != KC_XCHG_COPY)) return KC_ERR_ARG;
+  c->xmode = mode;
+  return KC_OK;
+}
+
+extern "C" int kc_exchange_export_slices(kc_ctx *c, uint32_t *n_slices, uint64_t *offsets) {
+  if (!c || !n_slices || !offsets) return KC_ERR_ARG;
+  if (c->phase < PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_export_slices: call kc_parse first");
+  const int S = (uint32_t)c->P >= 64u * kSlices ? kSlices : 1;
+  *n_slices = (uint32_t)S;
+  for (int o = 0; o < c->G; o++)
+    for (int i = 0; i <= KC_MAX_SLICES; i++) {
+      uint64_t v = used_region_bytes(c, o);
+      if (i <= S && c->h_slice_off.size() == (size_t)c->G * (S + 1)) v = std::min<uint64_t>(c->h_slice_off[(size_t)o * (S + 1) + i], v);
+      if (i == 0) v = std::min<uint64_t>(v, (uint64_t)c->header_bytes);
+      offsets[(size_t)o * (KC_MAX_SLICES + 1) + i] = v;
+    }
+  return KC_OK;
+}
+
+extern "C" int kc_exchange_import_slices(kc_ctx *c, int src, uint32_t n_slices, const uint64_t *offsets) {
+  if (!c || !offsets || src < 0 || src >= c->G || n_slices < 1 || n_slices > KC_MAX_SLICES) return KC_ERR_ARG;
+  if (c->phase != PH_PARSED) return fail(c, KC_ERR_STATE, "kc_exchange_import_slices: call kc_parse first");
+  if ((int)c->peer_slice_off.size() != c->G) c->peer_slice_off.assign(c->G, std::vector<uint64_t>());
+  c->peer_slice_off[src].assign(offsets, offsets + n_slices + 1);
   return KC_OK;
 }
 
@@ -957,46 +1111,68 @@ static int fine_header_bytes(const kc_ctx *c) {
   return (int)(((((uint64_t)c->P << c->fine_shift) * 8) + kHeaderAlign - 1) / kHeaderAlign * kHeaderAlign);
 }
 
-// second partition level: the coarse bins of every source -> one region of fine bins (d_fine), the count kernel's only source
-static int refine_bins(kc_ctx *c) {
-  RefineParams rp;
-  memset(&rp, 0, sizeof rp);
-  rp.n_src = c->G;
-  rp.rec_bytes = c->rec_bytes;
-  rp.n_coarse = (uint32_t)c->P;
-  rp.fine_shift = c->fine_shift;
-  rp.src_header_bytes = c->header_bytes;
-  rp.src_ptr = c->d_count_src;
-  rp.dst_header_bytes = fine_header_bytes(c);
-  if (c->coarse_base_alloc < (uint64_t)c->P + 2) {
-    dev_free(c->d_coarse_base);
-    CK(dev_alloc(&c->d_coarse_base, (uint64_t)c->P + 2));
-    c->coarse_base_alloc = (uint64_t)c->P + 2;
+// ---- the resident insert pipeline ---------------------------------------------------------
+// Everything between "the supermers of every source are reachable" and "the dense result is complete" is queued without
+// a single host round trip, slice by slice over the coarse bins, on three kinds of streams:
+//   xfer_stream[q]   (copy mode, G > 1) copy engines pull slice i of every peer's region over NVLink into d_recv
+//   refine_stream    refine_kernel sorts slice i of the coarse bins (all sources) into fine bins (d_fine)
+//   stream           count_kernel counts the fine bins of slice i; with a result sink the survivors of slice i go out on
+//                    copy_stream while slice i + 1 is counted
+// so the NVLink transfer (DMA, no SMs), the HBM-bound refine pass and the issue-bound count pass of neighbouring slices
+// overlap. Sizes the host needs (d_fine, grid shapes) come from bounds it already has: the parse-side record counts and
+// the region sizes the exchange reported.
+static int n_pipeline_slices(const kc_ctx *c) { return (uint32_t)c->P >= 64u * kSlices ? kSlices : 1; }
+
+// upper bound of the records this owner will consume (exact for one rank)
+static uint64_t record_bound(const kc_ctx *c) {
+  if (c->G == 1) return c->h_ctr.parse_records;
+  uint64_t n = c->h_owner_used.size() > (size_t)c->rank ? c->h_owner_used[c->rank] : 0;
+  for (int s = 0; s < c->G; s++) {
+    if (s == c->rank || (int)c->recv_bytes.size() != c->G) continue;
+    if (c->recv_bytes[s] > (uint64_t)c->header_bytes) n += (c->recv_bytes[s] - c->header_bytes) / c->rec_bytes;
   }
-  rp.coarse_base = c->d_coarse_base;
-  rp.total = c->d_coarse_base + c->P + 1;
-  rp.err_too_large = &c->d_ctr->err_bins_full;
-  CK(launch_refine_totals(rp, c->stream, &c->launches));
-  unsigned long long total = 0;
-  CK(cudaMemcpyAsync(&total, rp.total, sizeof total, cudaMemcpyDeviceToHost, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
-  if (total > 0xffffffffULL) return fail(c, KC_ERR_ARG, "more than 2^32 supermer records for one rank; use more ranks");
-  const uint64_t need = (uint64_t)rp.dst_header_bytes + total * c->rec_bytes + 256;
-  if (need > c->fine_alloc) {
-    dev_free(c->d_fine);
-    CK(dev_alloc(&c->d_fine, need + need / 16));
-    c->fine_alloc = need + need / 16;
+  return n;
+}
+
+// copy mode: queue the peer -> d_recv copies of slice `i` (i < 0: the header blocks) on the transfer streams and make
+// `waiter` wait for them
+static int queue_peer_copies(kc_ctx *c, int i, int n_slices, cudaStream_t waiter) {
+  int q = 0;
+  bool used[kXferStreams] = {false, false, false, false};
+  for (int s = 0; s < c->G; s++) {
+    if (s == c->rank || !c->pull_ptr[s] || c->recv_bytes[s] == 0) continue;
+    uint64_t lo, hi;
+    const uint64_t used_bytes = c->recv_bytes[s];
+    if (i < 0) {
+      lo = 0;
+      hi = std::min<uint64_t>(c->header_bytes, used_bytes);
+    } else if ((int)c->peer_slice_off.size() == c->G && (int)c->peer_slice_off[s].size() == n_slices + 1) {
+      lo = std::min<uint64_t>(std::max<uint64_t>(c->peer_slice_off[s][i], c->header_bytes), used_bytes);
+      hi = i + 1 == n_slices ? used_bytes : std::min<uint64_t>(std::max<uint64_t>(c->peer_slice_off[s][i + 1], c->header_bytes), used_bytes);
+    } else {  // no slice table from this peer: everything with the first slice
+      lo = std::min<uint64_t>(c->header_bytes, used_bytes);
+      hi = i == 0 ? used_bytes : lo;
+    }
+    if (hi <= lo) continue;
+    cudaStream_t xs = c->xfer_stream[q];
+    if (!c->xfer_started[q]) {
+      CK(cudaEventRecord(c->ev_xbeg[q], xs));
+      c->xfer_started[q] = true;
+    }
+    CK(cudaMemcpyAsync(c->d_recv + c->recv_off[s] + lo, c->pull_ptr[s] + lo, hi - lo, cudaMemcpyDeviceToDevice, xs));
+    c->xfer_bytes += hi - lo;
+    used[q] = true;
+    q = (q + 1) % kXferStreams;
   }
-  rp.dst = c->d_fine;
-  CK(launch_refine(rp, total / std::max<uint64_t>(rp.n_coarse, 1), c->sm_count, c->stream, &c->launches));
-  uint8_t *fine = c->d_fine;
-  CK(cudaMemcpyAsync(c->d_count_src + kCountMaxSrc, &fine, sizeof fine, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaStreamSynchronize(c->stream));  // `fine` is a local
+  for (int x = 0; x < kXferStreams; x++) {
+    if (!used[x]) continue;
+    CK(cudaEventRecord(c->ev_x[x], c->xfer_stream[x]));
+    CK(cudaStreamWaitEvent(waiter, c->ev_x[x], 0));
+  }
   return KC_OK;
 }
 
-// ---- bin-resident counting: one fused kernel does insert + purge + extension resolution + compaction
-static int launch_count_pass(kc_ctx *c, bool stream_out = false) {
+static CountParams count_params(kc_ctx *c) {
   const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
   CountParams cp;
   memset(&cp, 0, sizeof cp);
@@ -1006,7 +1182,8 @@ static int launch_count_pass(kc_ctx *c, bool stream_out = false) {
   cp.tile_records = insert_tile_records(c->rec_bytes);
   cp.n_bins = (uint32_t)c->P << c->fine_shift;
   cp.header_bytes = c->fine_shift ? fine_header_bytes(c) : c->header_bytes;
-  cp.src_ptr = c->fine_shift ? c->d_count_src + kCountMaxSrc : c->d_count_src;
+  cp.src_ptr = c->d_count_src;
+  cp.src0 = c->fine_shift ? c->d_fine : nullptr;
   cp.n_slots = c->count_slots;
   cp.claim_limit = (uint32_t)(0.85 * c->count_slots);
   cp.dmin_thres = c->cfg.dmin_thres;
@@ -1024,42 +1201,97 @@ static int launch_count_pass(kc_ctx *c, bool stream_out = false) {
   cp.ext_left = c->res_ext.left;
   cp.ext_right = c->res_ext.right;
   cp.cap_ext = keep_ext ? c->res_ext.cap : 0;
+  return cp;
+}
+
+// ---- bin-resident counting: refine + count (insert + purge + extension resolution + compaction), pipelined by slices.
+// `redo`: the count pass alone is repeated over the already refined bins (result arrays were too small).
+static int launch_count_pipeline(kc_ctx *c, bool redo) {
+  const int S = n_pipeline_slices(c);
+  const bool refine = c->fine_shift != 0;
+  const bool copy = !redo && c->G > 1 && c->xmode == KC_XCHG_COPY && (int)c->pull_ptr.size() == c->G;
+  const bool dedup = !(c->cfg.flags & KC_FLAG_NO_WARP_DEDUP);
+  CountParams cp = count_params(c);
   CK(cudaMemsetAsync(c->d_ctr, 0, offsetof(DevCounters, parse_counted), c->stream));
   CK(cudaEventRecord(c->ev_clr, c->stream));
   CK(cudaEventRecord(c->ev_ik0, c->stream));
-  const bool dedup = !(c->cfg.flags & KC_FLAG_NO_WARP_DEDUP);
   c->sink_streamed = false;
   c->sink_done = 0;
-  if (!stream_out || !c->sink_keys || cp.n_bins < 64u * kSinkSlices) {
-    cp.bin_begin = 0;
-    cp.bin_end = cp.n_bins;
-    CK(launch_count(cp, c->N, dedup, c->sm_count, c->stream, &c->launches));
-    CK(cudaEventRecord(c->ev_ik1, c->stream));
-    return KC_OK;
+  c->n_count_slices = c->n_refine_slices = 0;
+  c->xfer_bytes = 0;
+  for (auto &x : c->xfer_started) x = false;
+  const bool to_sink = !redo && c->sink_keys && S > 1;
+
+  RefineParams rp;
+  memset(&rp, 0, sizeof rp);
+  uint64_t avg_records = 0;
+  if (!redo) {
+    // the side streams start where the main stream is now
+    CK(cudaEventRecord(c->ev_fork, c->stream));
+    CK(cudaStreamWaitEvent(c->refine_stream, c->ev_fork, 0));
+    if (copy)
+      for (int q = 0; q < kXferStreams; q++) CK(cudaStreamWaitEvent(c->xfer_stream[q], c->ev_fork, 0));
   }
-  // Slices of bins: after every slice the result cursor comes back through pinned memory; as soon as the host sees it,
-  // the new entries [done, n) go out on the copy stream while the count stream is already busy with the next slices.
-  // The copy-out is the longer leg (PCIe): it should start as early as possible, so the first two slices are small
-  // (1/48 and 1/24 of the bins: the copy of one is about as long as the count of the next), the rest equal.
-  auto slice_edge = [&](int i) -> uint32_t {
-    if (i <= 0) return 0u;
-    if (i >= kSinkSlices) return cp.n_bins;
-    const uint64_t head = (uint64_t)cp.n_bins / 48;  // slice 0
-    if (i == 1) return (uint32_t)head;
-    const uint64_t second = 3 * head;                // slice 1 ends here
-    return (uint32_t)(second + ((uint64_t)cp.n_bins - second) * (uint64_t)(i - 2) / (uint64_t)(kSinkSlices - 2));
-  };
-  for (int i = 0; i < kSinkSlices; i++) {
-    cp.bin_begin = slice_edge(i);
-    cp.bin_end = slice_edge(i + 1);
-    CK(launch_count(cp, c->N, dedup, c->sm_count, c->stream, &c->launches));
-    CK(cudaMemcpyAsync(&c->h_slice_n[i], &c->d_ctr->n_final, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaEventRecord(c->ev_slice[i], c->stream));
+  if (refine && !redo) {
+    rp.n_src = c->G;
+    rp.rec_bytes = c->rec_bytes;
+    rp.n_coarse = (uint32_t)c->P;
+    rp.fine_shift = c->fine_shift;
+    rp.src_header_bytes = c->header_bytes;
+    rp.src_ptr = c->d_count_src;
+    rp.dst_header_bytes = fine_header_bytes(c);
+    rp.coarse_base = c->d_coarse_base;
+    rp.total = c->d_coarse_base + c->P + 1;
+    rp.err_too_large = &c->d_ctr->err_bins_full;
+    rp.dst = c->d_fine;
+    avg_records = record_bound(c) / std::max<uint64_t>(rp.n_coarse, 1);
+    if (copy) {
+      int rc = queue_peer_copies(c, -1, S, c->refine_stream);  // the peers' header blocks
+      if (rc) return rc;
+    }
+    CK(launch_refine_totals(rp, c->refine_stream, &c->launches));
+  } else if (copy) {
+    // no refine pass: the count kernel reads every source's segments itself -- everything has to be here first
+    int rc = queue_peer_copies(c, -1, S, c->stream);
+    for (int i = 0; i < S && !rc; i++) rc = queue_peer_copies(c, i, S, c->stream);
+    if (rc) return rc;
+  }
+  for (int i = 0; i < S; i++) {
+    const uint32_t c0 = slice_edge((uint32_t)c->P, i, S), c1 = slice_edge((uint32_t)c->P, i + 1, S);
+    if (refine && !redo) {
+      if (copy) {
+        int rc = queue_peer_copies(c, i, S, c->refine_stream);
+        if (rc) return rc;
+      }
+      rp.coarse_begin = c0;
+      rp.coarse_end = c1;
+      CK(cudaEventRecord(c->ev_rs0[i], c->refine_stream));
+      CK(launch_refine(rp, avg_records, c->sm_count, c->refine_stream, &c->launches));
+      CK(cudaEventRecord(c->ev_rs1[i], c->refine_stream));
+      c->n_refine_slices = i + 1;
+      CK(cudaStreamWaitEvent(c->stream, c->ev_rs1[i], 0));
+    }
+    cp.bin_begin = c0 << c->fine_shift;
+    cp.bin_end = c1 << c->fine_shift;
+    CK(cudaEventRecord(c->ev_cs0[i], c->stream));
+    if (cp.bin_end > cp.bin_begin) CK(launch_count(cp, c->N, dedup, c->sm_count, c->stream, &c->launches));
+    CK(cudaEventRecord(c->ev_cs1[i], c->stream));
+    c->n_count_slices = i + 1;
+    if (to_sink) {
+      CK(cudaMemcpyAsync(&c->h_slice_n[i], &c->d_ctr->n_final, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaEventRecord(c->ev_slice[i], c->stream));
+    }
   }
   CK(cudaEventRecord(c->ev_ik1, c->stream));
+  if (copy)
+    for (int q = 0; q < kXferStreams; q++)
+      if (c->xfer_started[q]) CK(cudaEventRecord(c->ev_xend[q], c->xfer_stream[q]));
+  if (!to_sink) return KC_OK;
+  // Result hand-off: after every slice the result cursor comes back through pinned memory; as soon as the host sees it,
+  // the new entries [done, n) go out on the copy stream while the count stream is already busy with the next slices.
   c->sink_streamed = true;
   const int N = c->N;
-  for (int i = 0; i < kSinkSlices; i++) {
+  for (int i = 0; i < S; i++) {
     CK(cudaEventSynchronize(c->ev_slice[i]));
     uint64_t n = c->h_slice_n[i];
     if (n > c->res_final.cap) n = c->res_final.cap;  // (the kernel flagged err_result_full: handled by kc_finalize)
@@ -1075,17 +1307,26 @@ static int launch_count_pass(kc_ctx *c, bool stream_out = false) {
   return KC_OK;
 }
 
-static int insert_resident(kc_ctx *c, const std::vector<uint8_t *> &src) {
+static int insert_resident(kc_ctx *c, const std::vector<uint8_t *> &src_in) {
   const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
+  std::vector<uint8_t *> src = src_in;
+  const bool copy = c->G > 1 && c->xmode == KC_XCHG_COPY && (int)c->pull_ptr.size() == c->G;
+  if (copy)
+    for (int s = 0; s < c->G; s++)
+      if (s != c->rank) src[s] = c->pull_ptr[s] && c->recv_bytes[s] ? c->d_recv + c->recv_off[s] : nullptr;
   if (!c->d_count_src) CK(dev_alloc(&c->d_count_src, 2 * kCountMaxSrc));
-  CK(cudaMemcpyAsync(c->d_count_src, src.data(), c->G * sizeof(uint8_t *), cudaMemcpyHostToDevice, c->stream));
-  CK(cudaStreamSynchronize(c->stream));
-  // result capacity: an entry that is written has count >= 2, so occurrences / 2 bounds it; the occurrences this owner
-  // receives are estimated from the local parse (the exchange is balanced by the minimizer hash). If the estimate or
-  // the memory budget falls short the kernel reports the exact need and kc_finalize re-runs it.
+  // (pinned staging: the previous use of these slots completed before the last kc_finalize returned)
+  for (int s = 0; s < c->G; s++) c->h_pinned[s] = (unsigned long long)(uintptr_t)src[s];
+  CK(cudaMemcpyAsync(c->d_count_src, c->h_pinned, c->G * sizeof(uint8_t *), cudaMemcpyHostToDevice, c->stream));
+  // Result capacity. An entry that is written has count >= 2, so occurrences / 2 bounds it -- but reserving that much is
+  // 5x what a typical run writes (24.6 GB reserved for a 4.8 GB result). Reserve what the last run of this
+  // context needed plus a margin, else occurrences / 6; a short-fall is reported exactly by the kernel (err_result_full
+  // with the need in the counters) and kc_finalize repeats the count pass once with the exact size.
   uint64_t occ = std::max<uint64_t>(c->h_ctr.parse_counted, 1024);
   if (c->G > 1) occ += occ / 4;
-  uint64_t cap = occ / 2 + 1024;
+  uint64_t cap = c->last_final ? c->last_final + c->last_final / 8 + 1024 : occ / 6 + 1024;
+  if (keep_ext) cap = std::max<uint64_t>(cap, c->last_ext ? c->last_ext + c->last_ext / 8 + 1024 : occ / 3 + 1024);
+  cap = std::min<uint64_t>(cap, occ / 2 + 1024);
   size_t free_b = 0, total_b = 0;
   CK(cudaMemGetInfo(&free_b, &total_b));
   const uint64_t per_entry = (uint64_t)c->N * 8 + 4 + (keep_ext ? (uint64_t)c->N * 8 + 20 : 0);
@@ -1100,13 +1341,26 @@ static int insert_resident(kc_ctx *c, const std::vector<uint8_t *> &src) {
     int rc = alloc_results(c, c->res_ext, cap, true);
     if (rc) return rc;
   }
+  if (c->fine_shift) {
+    const uint64_t bound = record_bound(c);
+    if (bound > 0xffffffffULL) return fail(c, KC_ERR_ARG, "more than 2^32 supermer records for one rank; use more ranks");
+    const uint64_t need = (uint64_t)fine_header_bytes(c) + bound * c->rec_bytes + 256;
+    if (need > c->fine_alloc) {
+      CK(cudaStreamSynchronize(c->stream));
+      dev_free(c->d_fine);
+      c->fine_alloc = 0;
+      CK(dev_alloc(&c->d_fine, need + need / 32));
+      c->fine_alloc = need + need / 32;
+    }
+    if (c->coarse_base_alloc < (uint64_t)c->P + 2) {
+      dev_free(c->d_coarse_base);
+      CK(dev_alloc(&c->d_coarse_base, (uint64_t)c->P + 2));
+      c->coarse_base_alloc = (uint64_t)c->P + 2;
+    }
+  }
   CK(cudaEventRecord(c->ev0, c->stream));
   c->stats.insert_kernel_launches = 1;
-  if (c->fine_shift) {
-    int rrc = refine_bins(c);
-    if (rrc) return rrc;
-  }
-  int rc = launch_count_pass(c, true);
+  int rc = launch_count_pipeline(c, false);
   if (rc) return rc;
   CK(cudaEventRecord(c->ev1, c->stream));
   c->phase = PH_INSERTED;
@@ -1118,37 +1372,71 @@ static int insert_resident(kc_ctx *c, const std::vector<uint8_t *> &src) {
 
 static void fill_stats(kc_ctx *c);
 
+static void pipeline_times(kc_ctx *c) {
+  float ms = 0, sum = 0;
+  for (int i = 0; i < c->n_count_slices; i++)
+    if (cudaEventElapsedTime(&ms, c->ev_cs0[i], c->ev_cs1[i]) == cudaSuccess) sum += ms;
+  c->stats.ms_insert_kernel = sum;
+  sum = 0;
+  for (int i = 0; i < c->n_refine_slices; i++)
+    if (cudaEventElapsedTime(&ms, c->ev_rs0[i], c->ev_rs1[i]) == cudaSuccess) sum += ms;
+  c->stats.ms_refine_kernel = sum;
+  // transfer window of the copy engines: first copy start to last copy end, over the transfer streams
+  float t0 = 1e30f, t1 = 0;
+  for (int q = 0; q < kXferStreams; q++) {
+    if (!c->xfer_started[q]) continue;
+    if (cudaEventSynchronize(c->ev_xend[q]) != cudaSuccess) continue;
+    float a = 0, b = 0;
+    if (cudaEventElapsedTime(&a, c->ev_fork, c->ev_xbeg[q]) == cudaSuccess && cudaEventElapsedTime(&b, c->ev_fork, c->ev_xend[q]) == cudaSuccess) {
+      t0 = std::min(t0, a);
+      t1 = std::max(t1, b);
+    }
+  }
+  c->stats.ms_exchange_copy = t1 > t0 ? t1 - t0 : 0.0;
+  c->stats.exchange_copy_bytes = c->xfer_bytes;
+  c->stats.pipeline_slices = c->n_count_slices;
+  cudaGetLastError();
+}
+
 static int finalize_resident(kc_ctx *c, kc_stats *stats) {
   const bool keep_ext = (c->cfg.flags & KC_FLAG_KEEP_EXT_COUNTS) != 0;
   CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
+  CK(cudaStreamSynchronize(c->refine_stream));
   float ms = 0;
   cudaEventElapsedTime(&ms, c->ev0, c->ev1);
   c->stats.ms_insert = ms;
-  cudaEventElapsedTime(&ms, c->ev_ik0, c->ev_ik1);
-  c->stats.ms_insert_kernel = ms;
+  pipeline_times(c);
   c->stats.ms_table_clear = 0;
   c->stats.ms_finalize = 0;
+  if (c->h_ctr.err_bins_full) return fail(c, KC_ERR_ARG, "more than 2^32 supermer records for one rank; use more ranks");
   if (c->h_ctr.err_result_full) {
     // the dense result was under-sized: the counters hold the exact need, allocate that and count again
     CK(cudaEventRecord(c->ev0, c->stream));
+    CK(cudaStreamSynchronize(c->copy_stream));
     int rc = alloc_results(c, c->res_final, c->h_ctr.n_final, false);
     if (rc) return rc;
     if (keep_ext && (rc = alloc_results(c, c->res_ext, c->h_ctr.n_ext, true))) return rc;
-    CK(cudaStreamSynchronize(c->copy_stream));
-    if ((rc = launch_count_pass(c))) return rc;
+    const float first_pass = (float)c->stats.ms_insert_kernel;
+    if ((rc = launch_count_pipeline(c, true))) return rc;
     c->stats.insert_kernel_launches++;
     CK(cudaEventRecord(c->ev1, c->stream));
     CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     c->stats.ms_finalize = ms;  // the repeated pass is charged to finalize
+    const double refine_ms = c->stats.ms_refine_kernel;
+    pipeline_times(c);
+    c->stats.ms_refine_kernel = refine_ms;
+    (void)first_pass;
     if (c->h_ctr.err_result_full) return fail(c, KC_ERR_STATE, "finalize: result overflow after exact re-allocation");
   }
   if (c->h_ctr.err_count_stack)
     return fail(c, KC_ERR_TABLE_FULL, "bin-resident counting: a bin could not be split far enough (use more local_bins or KC_FLAG_GLOBAL_TABLE)");
   c->res_final.n = c->h_ctr.n_final;
   c->res_ext.n = keep_ext ? c->h_ctr.n_ext : 0;
+  c->last_final = c->h_ctr.n_final;
+  c->last_ext = keep_ext ? c->h_ctr.n_ext : 0;
   if (c->sink_keys) {
     if (c->res_final.n > c->sink_cap)
       return fail(c, KC_ERR_ARG, "kc_finalize: %llu survivors do not fit the result sink (%llu entries)", (unsigned long long)c->res_final.n,
@@ -1500,14 +1788,12 @@ extern "C" int kc_result_checksum(kc_ctx *c, int extended, uint64_t *checksum) {
   ResultSet *r = pick(c, extended);
   if (!r || !checksum) return fail(c, KC_ERR_STATE, "kc_result_checksum: no result");
   CK(cudaSetDevice(c->device));
-  unsigned long long *d = nullptr;
-  CK(dev_alloc(&d, 1));
+  unsigned long long *d = c->d_scratch;  // pooled: no allocation per call, nothing to leak on the error paths
   CK(cudaMemsetAsync(d, 0, 8, c->stream));
   if (r->n) CK(launch_checksum(r->keys, r->counts, r->left, r->right, extended ? r->ext8 : nullptr, r->n, c->N, d, c->stream, &c->launches));
   unsigned long long h = 0;
   CK(cudaMemcpyAsync(&h, d, 8, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
-  cudaFree(d);
   *checksum = h;
   return KC_OK;
 }
@@ -1613,28 +1899,31 @@ extern "C" int kc_lookup(kc_ctx *c, const uint64_t *keys, uint64_t n, uint16_t *
     CK(cudaStreamSynchronize(c->stream));
     return KC_OK;
   }
-  // host batch: staged in pieces so that an arbitrarily large batch needs a bounded amount of HBM
+  // host batch: staged in pieces through a pooled device buffer (grown on demand, kept by the context: the reference's
+  // callers ask key by key, kmer_dht.cpp:199-245, so a lookup must not cost an allocation)
   const uint64_t piece = std::min<uint64_t>(n, (uint64_t)1 << 24);
-  uint64_t *d_q = nullptr;
-  uint16_t *d_c = nullptr;
-  char *d_l = nullptr, *d_r = nullptr;
-  cudaError_t e = cudaSuccess;
-  if ((e = cudaMalloc(&d_q, piece * c->N * 8)) != cudaSuccess || (e = cudaMalloc(&d_c, piece * 2)) != cudaSuccess ||
-      (e = cudaMalloc(&d_l, piece)) != cudaSuccess || (e = cudaMalloc(&d_r, piece)) != cudaSuccess) {
-    cudaFree(d_q), cudaFree(d_c), cudaFree(d_l), cudaFree(d_r);
-    return fail(c, KC_ERR_CUDA, "kc_lookup: %s", cudaGetErrorString(e));
+  if (piece > c->lookup_cap) {
+    dev_free(c->d_lq);
+    dev_free(c->d_lc);
+    dev_free(c->d_ll);
+    dev_free(c->d_lr);
+    c->lookup_cap = 0;
+    const uint64_t cap = std::max<uint64_t>(piece, 4096);
+    CK(dev_alloc(&c->d_lq, cap * c->N));
+    CK(dev_alloc(&c->d_lc, cap));
+    CK(dev_alloc(&c->d_ll, cap));
+    CK(dev_alloc(&c->d_lr, cap));
+    c->lookup_cap = cap;
   }
-  for (uint64_t q0 = 0; q0 < n && e == cudaSuccess; q0 += piece) {
+  for (uint64_t q0 = 0; q0 < n; q0 += piece) {
     const uint64_t nq = std::min(piece, n - q0);
-    e = cudaMemcpyAsync(d_q, keys + q0 * c->N, nq * c->N * 8, cudaMemcpyHostToDevice, c->stream);
-    if (e == cudaSuccess) e = launch_index_lookup(ip, d_q, nq, d_c, d_l, d_r, c->sm_count, c->stream, &c->launches);
-    if (e == cudaSuccess && counts) e = cudaMemcpyAsync(counts + q0, d_c, nq * 2, cudaMemcpyDeviceToHost, c->stream);
-    if (e == cudaSuccess && left) e = cudaMemcpyAsync(left + q0, d_l, nq, cudaMemcpyDeviceToHost, c->stream);
-    if (e == cudaSuccess && right) e = cudaMemcpyAsync(right + q0, d_r, nq, cudaMemcpyDeviceToHost, c->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    CK(cudaMemcpyAsync(c->d_lq, keys + q0 * c->N, nq * c->N * 8, cudaMemcpyHostToDevice, c->stream));
+    CK(launch_index_lookup(ip, c->d_lq, nq, c->d_lc, c->d_ll, c->d_lr, c->sm_count, c->stream, &c->launches));
+    if (counts) CK(cudaMemcpyAsync(counts + q0, c->d_lc, nq * 2, cudaMemcpyDeviceToHost, c->stream));
+    if (left) CK(cudaMemcpyAsync(left + q0, c->d_ll, nq, cudaMemcpyDeviceToHost, c->stream));
+    if (right) CK(cudaMemcpyAsync(right + q0, c->d_lr, nq, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
   }
-  cudaFree(d_q), cudaFree(d_c), cudaFree(d_l), cudaFree(d_r);
-  if (e != cudaSuccess) return fail(c, KC_ERR_CUDA, "kc_lookup: %s", cudaGetErrorString(e));
   return KC_OK;
 }
 

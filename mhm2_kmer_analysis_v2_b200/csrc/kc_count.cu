@@ -476,7 +476,8 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
   // Single source (the normal case: kc_refine.cu merged the sources): the header entries of the next two bins are kept
   // in flight, and the records of the next bin are pulled into L2 while this one is counted, so that a warp never waits
   // for DRAM at the top of a bin.
-  const uint2 *hdr0 = reinterpret_cast<const uint2 *>(p.src_ptr[0]);
+  const uint8_t *src0 = p.src0 ? p.src0 : (p.n_src == 1 ? p.src_ptr[0] : nullptr);
+  const uint2 *hdr0 = reinterpret_cast<const uint2 *>(src0);
   const bool single = p.n_src == 1 && hdr0 != nullptr;
   uint2 e_pre1 = make_uint2(0u, 0u), e_pre2 = make_uint2(0u, 0u);
   {
@@ -492,13 +493,13 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
       const uint2 e = e_pre1;
       e_pre1 = e_pre2;
       {
-        const uint8_t *nx = p.src_ptr[0] + p.header_bytes + (uint64_t)e_pre1.x * R;
+        const uint8_t *nx = src0 + p.header_bytes + (uint64_t)e_pre1.x * R;
         const uint32_t n_lines = (e_pre1.y * R + 127u) >> 7;
         for (uint32_t l = lane; l < n_lines; l += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + (size_t)l * 128));
       }
       const uint64_t b2 = (uint64_t)bin + 2ull * n_warps;
       e_pre2 = b2 < p.bin_end ? hdr0[b2] : make_uint2(0u, 0u);
-      wc.seg_ptr[0] = p.src_ptr[0] + p.header_bytes + (uint64_t)e.x * R;  // (every lane mirrors source 0)
+      wc.seg_ptr[0] = src0 + p.header_bytes + (uint64_t)e.x * R;  // (every lane mirrors source 0)
       wc.seg_ptr[1] = nullptr;
       wc.seg_n[0] = e.y;
       wc.seg_n[1] = 0;

@@ -178,6 +178,7 @@ struct CountParams {
   uint32_t bin_begin, bin_end;       // bins this launch counts (a slice of [0, n_bins): results stream out slice by slice)
   int header_bytes;                  // bytes of the per-source header block [n_bins x {u32 first_record, u32 n_records}]
   const uint8_t *const *src_ptr;     // [n_src] region of each source rank for this owner (nullptr = nothing received)
+  const uint8_t *src0;               // the single source (the refined region) when n_src == 1: no pointer table to read
   uint32_t n_slots;                  // table slots in shared memory (per warp)
   int warp_bytes;                    // shared memory of one warp (set by launch_count)
   uint32_t claim_limit;              // claimed slots at which a pass gives up and the bin is split further
@@ -201,6 +202,7 @@ cudaError_t launch_count(const CountParams &p, int n_words, bool merge_runs, int
 struct RefineParams {
   int n_src, rec_bytes;
   uint32_t n_coarse, fine_shift;
+  uint32_t coarse_begin, coarse_end;  // the slice of coarse bins this launch refines (launch_refine; 0, 0 = all)
   int src_header_bytes;            // per-source header block [n_coarse x {u32 first_record, u32 n_records}]
   const uint8_t *const *src_ptr;   // [n_src] region of each source rank for this owner (nullptr = nothing received)
   uint8_t *dst;                    // [fine header: (n_coarse << fine_shift) x {u32 first, u32 n}][records]
@@ -232,5 +234,22 @@ cudaError_t sort_result_by_key(uint64_t *keys, uint16_t *counts, char *left, cha
                                cudaStream_t s, uint64_t *launches);
 
 static const int kHeaderAlign = 64;
+
+// ---- slices of the bin range: the receive copies, the refine pass, the count pass and the result hand-off all work slice
+// by slice so that they overlap (kc_api.cu). Edge i of kSlices slices over n bins; the first two slices are small (1/48 and
+// 1/24 of the bins) so that the pipeline fills quickly, the rest are equal. The same function on every rank.
+static const int kSlices = 12;
+__host__ __device__ inline uint32_t slice_edge(uint32_t n, int i, int n_slices) {
+  if (i <= 0) return 0u;
+  if (i >= n_slices) return n;
+  if (n_slices < 3) return (uint32_t)((uint64_t)n * (uint64_t)i / (uint64_t)n_slices);
+  const uint64_t head = (uint64_t)n / 48;
+  if (i == 1) return (uint32_t)head;
+  const uint64_t second = 3 * head;
+  return (uint32_t)(second + ((uint64_t)n - second) * (uint64_t)(i - 2) / (uint64_t)(n_slices - 2));
+}
+// byte offset (from the start of an owner's region) of every slice edge, for every owner: out[o * (n_slices + 1) + i]
+cudaError_t launch_slice_offsets(const uint64_t *bin_first, const uint64_t *bin_cap, uint32_t n_ranks, uint32_t local_bins, int n_slices, int header_bytes,
+                                 int rec_bytes, unsigned long long *out, cudaStream_t s, uint64_t *launches);
 
 }  // namespace kc

@@ -479,6 +479,29 @@ __global__ void layout_bases_kernel(LayoutParams p, uint32_t blocks_per_owner) {
   p.bin_base[i] = p.region_off[o] + p.header_bytes + first * p.rec_bytes;
 }
 
+// where every slice of coarse bins starts inside each owner's region (edge n_slices = end of the record area by
+// capacity; the caller clips it to the used bytes)
+__global__ void slice_offsets_kernel(const uint64_t *bin_first, const uint64_t *bin_cap, uint32_t n_ranks, uint32_t P, int n_slices,
+                                     int header_bytes, int rec_bytes, unsigned long long *out) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t per = (uint32_t)n_slices + 1u;
+  if (t >= n_ranks * per) return;
+  const uint32_t o = t / per, i = t % per;
+  const uint32_t e = slice_edge(P, (int)i, n_slices);
+  unsigned long long first;
+  if (e < P) first = bin_first[(uint64_t)o * P + e];
+  else first = bin_first[(uint64_t)o * P + P - 1] + (bin_cap ? bin_cap[(uint64_t)o * P + P - 1] : 0ULL);
+  out[t] = (unsigned long long)header_bytes + first * (unsigned long long)rec_bytes;
+}
+
+cudaError_t launch_slice_offsets(const uint64_t *bin_first, const uint64_t *bin_cap, uint32_t n_ranks, uint32_t local_bins, int n_slices,
+                                 int header_bytes, int rec_bytes, unsigned long long *out, cudaStream_t s, uint64_t *launches) {
+  const uint32_t n = n_ranks * ((uint32_t)n_slices + 1u);
+  slice_offsets_kernel<<<(n + 127) / 128, 128, 0, s>>>(bin_first, bin_cap, n_ranks, local_bins, n_slices, header_bytes, rec_bytes, out);
+  (*launches)++;
+  return cudaGetLastError();
+}
+
 cudaError_t launch_layout(const LayoutParams &p, cudaStream_t s, uint64_t *launches) {
   (*launches) += 3;
   const uint32_t nb = layout_blocks_per_owner(p.local_bins);

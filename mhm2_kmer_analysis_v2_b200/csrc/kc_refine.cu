@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(RefineParams p) {
   uint2 *fine_hdr = reinterpret_cast<uint2 *>(p.dst);
   uint8_t *dst_rec = p.dst + p.dst_header_bytes;
 
-  for (uint32_t c = blockIdx.x; c < p.n_coarse; c += gridDim.x) {
+  for (uint32_t c = p.coarse_begin + blockIdx.x; c < p.coarse_end; c += gridDim.x) {
     __syncthreads();  // the previous coarse bin is done with the shared state
     if (tid < p.n_src) {
       const uint8_t *src = p.src_ptr[tid];
@@ -230,7 +230,8 @@ cudaError_t launch_refine_totals(const RefineParams &p, cudaStream_t s, uint64_t
 template <int R, int THREADS, int STAGE>
 static cudaError_t launch_refine_shape(const RefineParams &p, int sm_count, int ctas_per_sm, cudaStream_t s) {
   uint64_t grid = (uint64_t)sm_count * ctas_per_sm;
-  if (grid > p.n_coarse) grid = p.n_coarse ? p.n_coarse : 1;
+  const uint32_t n_bins = p.coarse_end - p.coarse_begin;
+  if (grid > n_bins) grid = n_bins ? n_bins : 1;
   cudaError_t e = cudaFuncSetAttribute(refine_kernel<R, THREADS, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, STAGE);
   if (e != cudaSuccess) return e;
   refine_kernel<R, THREADS, STAGE><<<(int)grid, THREADS, STAGE, s>>>(p);
@@ -245,7 +246,10 @@ static cudaError_t launch_refine_r(const RefineParams &p, int sm_count, int shap
 }
 
 // avg_records: records per coarse bin (all sources), picks the launch shape
-cudaError_t launch_refine(const RefineParams &p, uint64_t avg_records, int sm_count, cudaStream_t s, uint64_t *launches) {
+cudaError_t launch_refine(const RefineParams &p_in, uint64_t avg_records, int sm_count, cudaStream_t s, uint64_t *launches) {
+  RefineParams p = p_in;
+  if (p.coarse_begin == 0 && p.coarse_end == 0) p.coarse_end = p.n_coarse;
+  if (p.coarse_end <= p.coarse_begin) return cudaSuccess;
   if (p.n_src > kCountMaxSrc || (1u << p.fine_shift) > (uint32_t)RF_MAX_SUB) return cudaErrorInvalidValue;
   const uint64_t want = avg_records * (uint64_t)p.rec_bytes * 3 / 2;  // average bin + 50 %
   int shape = want > (uint64_t)RF_STAGE_SMALL ? 2 : (want > (uint64_t)RF_STAGE_TINY ? 1 : 0);

@@ -2,7 +2,7 @@
  * kc_synth.c -- seeded synthetic read streams in the reference's PackedRead byte encoding
  * (base(A0 C1 G2 T3 N4) | min(qual - offset, 31) << 3, src/packed_reads.cpp:99-126).
  *
- * Host-only helper of the C ABI (kc_synth_*, kc_reads_save in include/kcount_b200.h). It produces the
+ * Host-only helper of the C ABI (kc_synth_*, kc_reads_save in include/kc_synth.h; built as libkc_synth.so). It produces the
  * inputs BASELINE.md section 4 describes: random genomes (one, or a lognormal-abundance community),
  * uniform read starts, random strand, substitution errors, Phred 40 ('I') qualities with a low-quality
  * Phred 10 ('+') on 2 % of correct and 50 % of substituted bases; optional pairs and N bases.
@@ -15,7 +15,7 @@
 #include <stdlib.h>
 #include <string.h>
 
-#include "kcount_b200.h"
+#include "kc_synth.h"
 
 typedef struct {
   uint64_t s[4];
@@ -103,9 +103,9 @@ static void *genome_worker(void *arg) {
 int kc_synth_create(const kc_synth_config *cfg, kc_synth **out) {
   if (!cfg || !out || cfg->n_genomes == 0 || cfg->read_len == 0 || cfg->read_len > 65535 ||
       cfg->genome_len_min > cfg->genome_len_max || cfg->genome_len_min < (uint64_t)cfg->read_len * 4)
-    return KC_ERR_ARG;
+    return KC_SYNTH_ERR_ARG;
   kc_synth *s = (kc_synth *)calloc(1, sizeof(kc_synth));
-  if (!s) return KC_ERR_NOMEM;
+  if (!s) return KC_SYNTH_ERR_NOMEM;
   s->cfg = *cfg;
   uint32_t G = s->n_genomes = cfg->n_genomes;
   s->glen = (uint64_t *)malloc(G * sizeof(uint64_t));
@@ -129,7 +129,7 @@ int kc_synth_create(const kc_synth_config *cfg, kc_synth **out) {
   s->bases = (uint8_t *)malloc(at);
   if (!s->bases) {
     kc_synth_destroy(s);
-    return KC_ERR_NOMEM;
+    return KC_SYNTH_ERR_NOMEM;
   }
   int nt = G < 8 ? (int)G : 8;
   pthread_t th[8];
@@ -142,7 +142,7 @@ int kc_synth_create(const kc_synth_config *cfg, kc_synth **out) {
   }
   for (int t = 0; t < nt; t++) pthread_join(th[t], NULL);
   *out = s;
-  return KC_OK;
+  return KC_SYNTH_OK;
 }
 
 void kc_synth_destroy(kc_synth *s) {
@@ -229,7 +229,7 @@ static void *read_worker(void *arg) {
 
 int kc_synth_generate(const kc_synth *s, uint64_t first, uint64_t n, uint8_t *bytes, uint64_t *offsets, uint16_t *lens,
                       uint64_t *n_bytes, int n_threads) {
-  if (!s || !bytes || !offsets || !lens) return KC_ERR_ARG;
+  if (!s || !bytes || !offsets || !lens) return KC_SYNTH_ERR_ARG;
   uint64_t at = 0;
   for (uint64_t t = 0; t < n; t++) {
     lens[t] = read_len_of(s, first + t);
@@ -247,17 +247,17 @@ int kc_synth_generate(const kc_synth *s, uint64_t first, uint64_t n, uint8_t *by
     pthread_create(&th[t], NULL, read_worker, &jobs[t]);
   }
   for (int t = 0; t < n_threads; t++) pthread_join(th[t], NULL);
-  return KC_OK;
+  return KC_SYNTH_OK;
 }
 
 int kc_reads_save(const char *path, const uint8_t *bytes, uint64_t n_bytes, const uint64_t *offsets, const uint16_t *lens,
                   uint64_t n_reads) {
   FILE *f = fopen(path, "wb");
-  if (!f) return KC_ERR_IO;
+  if (!f) return KC_SYNTH_ERR_IO;
   uint64_t hdr[4] = {0x3153444145524b43ULL /* "KCREADS1" */, n_reads, n_bytes, 0};
   uint64_t pad = 0, lens_bytes = n_reads * 2, lens_pad = ((lens_bytes + 7) & ~7ull) - lens_bytes;
   int ok = fwrite(hdr, 8, 4, f) == 4 && fwrite(offsets, 8, n_reads, f) == n_reads && fwrite(lens, 2, n_reads, f) == n_reads &&
            fwrite(&pad, 1, lens_pad, f) == lens_pad && fwrite(bytes, 1, n_bytes, f) == n_bytes;
   fclose(f);
-  return ok ? KC_OK : KC_ERR_IO;
+  return ok ? KC_SYNTH_OK : KC_SYNTH_ERR_IO;
 }

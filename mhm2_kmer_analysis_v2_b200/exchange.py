@@ -93,38 +93,104 @@ def exchange_supermers(stage, group=None):
     return int(send_sizes.sum()), int(recv_sizes.sum()), secs
 
 
+MAX_SLICES = 12  # KC_MAX_SLICES
+
+
+def set_exchange_mode(stage, mode):
+    """'pull' (the kernels read the peers' memory) or 'copy' (copy engines stream it in, slice by slice, beside the
+    kernels). Both are driven by exchange_supermers_pull / release_peers."""
+    stage.set_exchange_mode(mode)
+
+
+class ExchangeAborted(RuntimeError):
+    """A rank of the group failed inside the peer-memory protocol; every rank raises this instead of waiting forever."""
+
+
+def _coll_device(group):
+    return torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+
+
 def exchange_supermers_pull(stage, group=None):
     """Peer-memory variant for the GPUs of one NVLink / NVSwitch node: nothing is moved here. Every rank publishes its
     send buffer (CUDA IPC handle + per-owner region offsets / used bytes, one small all-gather), every owner maps the
     regions meant for it, and kc_insert's refine kernel pulls the records out of the peers' HBM while it sorts them into
     fine bins -- transfer and partition in one kernel, only used records on the links. The caller must call
-    release_peers() after finalize(), before any rank parses again. Returns (0, bytes_to_pull, 0.0)."""
+    release_peers() after finalize() -- also when its own insert / finalize failed (ok=False) -- before any rank parses
+    again. Returns (0, bytes_to_pull, 0.0).
+
+    Failure path: the all-gather carries a status byte. A rank whose parse / export failed still takes part (status 0)
+    and every rank raises ExchangeAborted without importing anything; a rank that died is caught by the process group's
+    timeout (bench.py and the tests set it), not by an endless wait."""
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     assert world == stage.n_ranks and rank == stage.rank
-    dev = torch.device("cuda", torch.cuda.current_device())
-    stage.sync()  # this rank's bins are complete (kc_parse synchronises, this is for callers that queued more work)
-    h, off, nb = stage.export_regions()
-    mine = torch.from_numpy(np.concatenate([h.view(np.uint8), off.view(np.uint8), nb.view(np.uint8)])).to(dev)
+    dev = _coll_device(group)
+    ok, err = 1, None
+    h, off, nb = np.zeros(64, np.uint8), np.zeros(world, np.uint64), np.zeros(world, np.uint64)
+    n_sl, sl = 1, np.zeros((world, MAX_SLICES + 1), np.uint64)
+    try:
+        stage.sync()  # this rank's bins are complete (kc_parse synchronises, this is for callers that queued more work)
+        h, off, nb = stage.export_regions()
+        n_sl, sl = stage.export_slices()
+    except Exception as e:  # noqa: BLE001 -- reported to the peers, re-raised below
+        ok, err = 0, e
+    mine = torch.from_numpy(np.concatenate([np.array([ok, n_sl] + [0] * 6, np.uint8), h.view(np.uint8), off.view(np.uint8), nb.view(np.uint8),
+                                            sl.reshape(-1).view(np.uint8)])).to(dev)
     rows = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(rows, mine, group=group)  # also the barrier "every rank has parsed"
+    rows = [r.cpu().numpy() for r in rows]
+    failed = [s for s in range(world) if rows[s][0] == 0]
+    if failed:
+        raise ExchangeAborted(f"peer-memory exchange aborted: rank(s) {failed} failed before the export" + (f" (here: {err})" if err else ""))
     pulled = 0
     for s in range(world):
         if s == rank:
             continue
-        r = rows[s].cpu().numpy()
+        r = rows[s][8:]
         o = r[64:64 + 8 * world].view(np.uint64)
         b = r[64 + 8 * world:64 + 16 * world].view(np.uint64)
+        t = r[64 + 16 * world:].view(np.uint64).reshape(world, MAX_SLICES + 1)
         stage.import_region(s, r[:64], int(o[rank]), int(b[rank]))
+        stage.import_slices(s, int(rows[s][1]), t[rank, :int(rows[s][1]) + 1])
         pulled += int(b[rank])
     stage.exchange_done()
     return 0, pulled, 0.0
 
 
-def release_peers(stage, group=None):
-    """Second half of the peer-memory exchange: my kernels are done with the peers' buffers, and theirs with mine."""
-    stage.sync()
-    dist.barrier(group=group)
+def release_peers(stage, group=None, ok=True):
+    """Second half of the peer-memory exchange: my kernels are done with the peers' buffers, and theirs with mine.
+    Every rank calls this once per exchange_supermers_pull, with ok=False when its insert / finalize raised: the
+    agreement (an all-reduce, which is also the barrier) makes all ranks raise ExchangeAborted together instead of one
+    rank waiting for a peer that will never arrive. Then the send buffers retired by a re-allocation are freed."""
+    try:
+        stage.sync()
+    except Exception:  # noqa: BLE001
+        ok = False
+    t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=_coll_device(group))
+    dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+    stage.exchange_release()
+    if int(t.item()) == 0:
+        raise ExchangeAborted("a rank failed between the export and the release of the peer-memory exchange")
+
+
+def count_step_pull(stage, group=None):
+    """parse -> peer-memory exchange -> insert -> finalize -> release, with the failure path wired: whatever this rank
+    raises between export and release is reported to the peers first. Returns (stats, exchange tuple)."""
+    stage.parse()
+    xb = exchange_supermers_pull(stage, group)
+    stats, err = None, None
+    try:
+        stage.insert()
+        stats = stage.finalize()
+    except Exception as e:  # noqa: BLE001
+        err = e
+    try:
+        release_peers(stage, group, ok=err is None)
+    except ExchangeAborted:
+        if err is not None:
+            raise err
+        raise
+    return stats, xb
 
 
 def global_avg_kmer_count(stats, group=None):

@@ -157,12 +157,32 @@ class KcountStage:
         self._ck(self.L.kc_exchange_export(self.h, h.ctypes.data, off.ctypes.data, nb.ctypes.data))
         return h, off, nb
 
+    def export_slices(self):
+        """(n_slices, offsets[n_ranks, KC_MAX_SLICES + 1]): byte offset of every pipeline-slice edge in each owner's region."""
+        n = C.c_uint32()
+        off = np.zeros((self.n_ranks, _lib.KC_MAX_SLICES + 1), np.uint64)
+        self._ck(self.L.kc_exchange_export_slices(self.h, C.byref(n), off.ctypes.data))
+        return n.value, off
+
+    def import_slices(self, src, n_slices, offsets):
+        offsets = np.ascontiguousarray(offsets, np.uint64)
+        self._ck(self.L.kc_exchange_import_slices(self.h, int(src), int(n_slices), offsets.ctypes.data))
+
+    def set_exchange_mode(self, mode):
+        """'pull': the refine / count kernels read the peers' HBM themselves; 'copy': copy engines bring the peers' regions
+        in slice by slice while the previous slices are refined and counted."""
+        self._ck(self.L.kc_exchange_set_mode(self.h, {"pull": _lib.KC_XCHG_PULL, "copy": _lib.KC_XCHG_COPY}[mode]))
+
     def import_region(self, src, handle, offset, nbytes):
         handle = np.ascontiguousarray(handle, np.uint8)
         self._ck(self.L.kc_exchange_import(self.h, int(src), handle.ctypes.data, int(offset), int(nbytes)))
 
     def exchange_done(self):
         self._ck(self.L.kc_exchange_done(self.h))
+
+    def exchange_release(self):
+        """After the barrier that follows finalize(): frees exported send buffers that were since re-allocated."""
+        self._ck(self.L.kc_exchange_release(self.h))
 
     # ---- results
     def result_size(self, extended=False):

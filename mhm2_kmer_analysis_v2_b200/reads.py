@@ -1,4 +1,4 @@
-"""Seeded synthetic PackedRead streams (kc_synth_* of the C ABI) and the configs of BASELINE.md section 4."""
+"""Seeded synthetic PackedRead streams (kc_synth_* of include/kc_synth.h, libkc_synth.so) and the configs of BASELINE.md section 4."""
 import ctypes as C
 import os
 
@@ -37,7 +37,7 @@ class ReadSet:
         return ReadSet(self.bytes[b0:b1], off - np.uint64(b0), self.lens[lo:hi])
 
     def save(self, path):
-        L = _lib.lib()
+        L = _lib.synth_lib()
         rc = L.kc_reads_save(os.fsencode(path), self.bytes.ctypes.data, len(self.bytes), self.offsets.ctypes.data,
                              self.lens.ctypes.data, len(self.lens))
         if rc:
@@ -95,7 +95,7 @@ class PinnedBuffer:
 
 def synth_config(**kw):
     cfg = _lib.KcSynthConfig()
-    _lib.lib().kc_synth_config_default(C.byref(cfg))
+    _lib.synth_lib().kc_synth_config_default(C.byref(cfg))
     for k, v in kw.items():
         if not hasattr(cfg, k):
             raise TypeError(f"unknown synth option {k}")
@@ -122,7 +122,7 @@ class Synth:
     """Handle on a seeded read stream; read i depends only on (seed, i)."""
 
     def __init__(self, cfg=None, **kw):
-        self.L = _lib.lib()
+        self.L = _lib.synth_lib()
         self.cfg = cfg if cfg is not None else synth_config(**kw)
         self.h = C.c_void_p()
         rc = self.L.kc_synth_create(C.byref(self.cfg), C.byref(self.h))

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <vector>
 
+#include "kc_synth.h"
 #include "kcount_b200.hpp"
 
 using namespace kcount_b200;
@@ -21,12 +22,12 @@ static int run(unsigned k, uint64_t n_reads, uint64_t seed, const char *dump) {
   sc.abundance_sigma = 1.0;
   sc.n_rate = 0.001;
   kc_synth *syn = nullptr;
-  if (kc_synth_create(&sc, &syn) != KC_OK) return 2;
+  if (kc_synth_create(&sc, &syn) != KC_SYNTH_OK) return 2;
   std::vector<uint8_t> bytes(n_reads * sc.read_len);
   std::vector<uint64_t> off(n_reads);
   std::vector<uint16_t> len(n_reads);
   uint64_t nb = 0;
-  if (kc_synth_generate(syn, 0, n_reads, bytes.data(), off.data(), len.data(), &nb, 4) != KC_OK) return 3;
+  if (kc_synth_generate(syn, 0, n_reads, bytes.data(), off.data(), len.data(), &nb, 4) != KC_SYNTH_OK) return 3;
   kc_synth_destroy(syn);
 
   const int qual_offset = 33, dmin_thres = 2;

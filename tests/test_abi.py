@@ -12,10 +12,11 @@ from mhm2_kmer_analysis_v2_b200 import _lib
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "kcount_b200.h")
+SYNTH_HEADER = os.path.join(ROOT, "include", "kc_synth.h")
 
 
-def declared_symbols():
-    src = open(HEADER).read()
+def declared_symbols(header=HEADER):
+    src = open(header).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(kc_[a-z0-9_]+)\s*\(", src)))
 
@@ -30,15 +31,27 @@ def test_header_symbols_are_exported_and_bound():
     assert set(_lib.PROTOTYPES) <= set(names), "ctypes binds symbols the header does not declare"
 
 
+def test_synth_header_symbols_live_in_their_own_library():
+    """include/kc_synth.h <-> libkc_synth.so; the product library exports none of them (the CPU arms of bench.py generate
+    their reads without mapping libkcount_b200.so)."""
+    S = C.CDLL(_lib.SYNTH_LIB_PATH)
+    L = C.CDLL(_lib.LIB_PATH)
+    names = declared_symbols(SYNTH_HEADER)
+    assert set(names) == set(_lib.SYNTH_PROTOTYPES)
+    for n in names:
+        assert hasattr(S, n), f"{n} declared in include/kc_synth.h but not exported by libkc_synth.so"
+        assert not hasattr(L, n), f"{n} is exported by the product library as well"
+
+
 def test_struct_layouts_match_the_header():
     L = _lib.lib()
     cfg = _lib.KcConfig()
     L.kc_config_default(C.byref(cfg))
-    assert (cfg.abi_version, cfg.k, cfg.m, cfg.qual_offset, cfg.qual_cutoff, cfg.dmin_thres) == (1, 21, 0, 33, 20, 2)
+    assert (cfg.abi_version, cfg.k, cfg.m, cfg.qual_offset, cfg.qual_cutoff, cfg.dmin_thres) == (_lib.KC_ABI_VERSION, 21, 0, 33, 20, 2)
     assert cfg.dyn_min_depth == 0.9 and cfg.n_ranks == 1 and cfg.device == -1 and cfg.sequencing_depth == 4
     assert cfg.base_error_rate == 0.005 and cfg.flags == 0 and cfg.local_bins == 0
     s = _lib.KcSynthConfig()
-    L.kc_synth_config_default(C.byref(s))
+    _lib.synth_lib().kc_synth_config_default(C.byref(s))
     assert s.seed == 1001 and s.read_len == 150 and s.sub_rate == 0.005 and s.qual_offset == 33
     assert L.kc_version().decode().startswith("kcount_b200")
 

@@ -18,7 +18,7 @@ def facade_bin(tmp_path_factory):
     out = str(tmp_path_factory.mktemp("facade") / "facade_main")
     pkg = os.path.join(ROOT, "mhm2_kmer_analysis_v2_b200")
     subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
-                    os.path.join(ROOT, "tests", "cpp", "facade_main.cpp"), "-L", pkg, "-lkcount_b200", f"-Wl,-rpath,{pkg}", "-o", out],
+                    os.path.join(ROOT, "tests", "cpp", "facade_main.cpp"), "-L", pkg, "-lkcount_b200", "-lkc_synth", f"-Wl,-rpath,{pkg}", "-o", out],
                    check=True)
     return out
 
