@@ -1,19 +1,25 @@
 #!/usr/bin/env python
 """Headline benchmark of the k-mer analysis stage (BASELINE.json metric: counted k-mers per second).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload C1..C5 --k K --m M --filter 0|1]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-Workload = BASELINE config 2 ("C2"): seeded synthetic metagenome mix, 100 random genomes of 1-5 Mbp with lognormal(0,1)
-abundance, 20 M x 150 bp reads PER GPU (weak scaling: rank r takes reads [r*20M, (r+1)*20M) of the one seeded stream),
-0.5 % substitutions, k = 33 (two key words), singleton filter off, min depth 2.
+Headline workload = BASELINE config 2 ("C2"): seeded synthetic metagenome mix, 100 random genomes of 1-5 Mbp with
+lognormal(0,1) abundance, 20 M x 150 bp reads PER GPU (weak scaling: rank r takes reads [r*20M, (r+1)*20M) of the one seeded
+stream), 0.5 % substitutions, k = 33 (two key words), singleton filter off, min depth 2. The other BASELINE configs
+(C1 k=21; C2 k=21/55; C3 paired k=21/33/55; C4 k=77/99 with m=15 and m=27; C5 1 % error, filter on / off) are run at reduced
+steps after the headline and reported under "configs" in the same JSON line (--configs none|auto|all).
 
 One step = one complete pass of the hot path over the rank's reads: kc_reset, supermer extraction (kc_parse), the owner
-exchange when N > 1 (NCCL all-to-all), table insert (kc_insert), purge/extension/compaction (kc_finalize).
+exchange when N > 1 (peer-memory pull, copy engines or NCCL all-to-all), refine + count (kc_insert), kc_finalize.
+  parity_check  before anything is timed: a small seeded read set goes through the SAME path (exchange mode, table variant,
+           k, m) on all ranks; the order-independent result checksum summed over the owners must equal the CPU checker's
+           (oracle/_ref/kcount_ref = the reference's own sources, else oracle/libkcount_oracle.so). Mismatch = exit 1.
   value    reads resident in HBM at the start of the step, result left in HBM; timed on the device (CUDA events on the
            stage's stream, host gaps included), max over ranks.
-  e2e      same stage through the C ABI with HOST buffers: pinned reads -> kc_add_reads (H2D) -> run -> kc_result_copy of
-           the final (k-mer, count, left, right) arrays into pinned host memory (D2H); wall clock between device syncs.
+  e2e      same stage through the C ABI with HOST buffers: pinned reads -> kc_add_reads (H2D) -> run -> survivors into a
+           pinned host sink (D2H); wall clock between device syncs. --e2e-depth 2 (default): two stage objects, two host
+           threads, so the H2D of one job overlaps the D2H of the other (PCIe is full duplex); depth 1 = strictly serial.
   roofline the dominant kernel alone (count_kernel = insert + purge + extension resolution over shared-memory tables;
            insert_kernel with --filter 1 / --global-table): B_alg(k) ALGORITHMIC bytes per counted k-mer x
            k-mers per launch / its CUDA-event time, against MEASURED_PEAKS.json hbm_gbs.
@@ -34,12 +40,19 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-K_DEFAULT = 33
-READS_PER_GPU = 20_000_000
 READ_LEN = 150
-WORKLOAD = "C2"
 METRIC = "counted_kmers_per_sec"
 UNIT = "kmers/s"
+
+# BASELINE.json configs. reads = per GPU (weak scaling) unless total_reads is set (C4: "the 20M-read mix at
+# 2/4/8 GPUs" is one fixed read set split over the GPUs)
+WORKLOADS = {
+    "C1": dict(k=21, reads_per_gpu=1_000_000, desc="1 M x 150 bp reads from one random 5 Mbp genome, 0.5% substitutions, seed 1001"),
+    "C2": dict(k=33, reads_per_gpu=20_000_000, desc="synthetic metagenome mix, 100 genomes 1-5 Mbp lognormal(0,1), 0.5% substitutions, seed 2002"),
+    "C3": dict(k=21, reads_per_gpu=25_000_000, desc="ArcticSynth-shaped paired reads (insert ~N(300,30)), 100-genome mix, 0.5% substitutions, seed 3003"),
+    "C4": dict(k=77, reads_per_gpu=20_000_000, total_reads=20_000_000, desc="long-k path on the 20 M-read C2 mix (multi-word keys), seed 2002"),
+    "C5": dict(k=21, reads_per_gpu=20_000_000, desc="high-error reads: the C2 community at 1% substitutions, seed 5005"),
+}
 
 
 def b_alg(k, read_len=READ_LEN):
@@ -57,13 +70,26 @@ def load_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def config_dict(args, n_gpus):
+def profile_traffic(k, kernel_variant):
+    """DRAM bytes per counted k-mer of the dominant kernel from the committed `ncu --set full` capture of this round
+    (profiles/r02_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of one launch / its k-mers), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
+            tj = json.load(f)
+        e = tj.get(f"{kernel_variant}_k{k}")
+        return (e["dram_bytes_per_counted_kmer"], e.get("source")) if e else (None, None)
+    except Exception:
+        return None, None
+
+
+def config_dict(spec, n_gpus):
+    w = WORKLOADS[spec["workload"]]
     return {
-        "workload": f"{WORKLOAD}: synthetic metagenome mix, 100 genomes 1-5 Mbp lognormal(0,1), {args.reads_per_gpu} x {READ_LEN} bp reads per GPU, "
-                    f"0.5% substitutions, seed 2002, k={args.k}, kcount stage only",
-        "k": args.k, "reads_per_gpu": args.reads_per_gpu, "read_len": READ_LEN, "n_gpus": n_gpus, "filter": bool(args.filter),
-        "dmin_thres": 2, "parallelism": f"owner-partitioned x{n_gpus}" if n_gpus > 1 else "single GPU",
-        "l2": "inputs (reads 3 GB, supermer records 13 GB, result 5 GB per GPU) each far larger than the 126 MB L2; no explicit flush",
+        "workload": f"{spec['workload']}: {w['desc']}, {spec['reads_per_gpu']} x {READ_LEN} bp reads per GPU, k={spec['k']}, kcount stage only",
+        "k": spec["k"], "m": spec["m"] or "reference rule clamp(2k/3+1,15,27)", "reads_per_gpu": spec["reads_per_gpu"], "read_len": READ_LEN,
+        "n_gpus": n_gpus, "filter": bool(spec["filter"]), "global_table": bool(spec["global_table"]), "dmin_thres": 2,
+        "parallelism": f"owner-partitioned x{n_gpus}" if n_gpus > 1 else "single GPU",
+        "l2": "inputs (reads, supermer records, result: GBs per GPU) each far larger than the 126 MB L2; no explicit flush",
     }
 
 
@@ -131,25 +157,28 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def cpu_reference_run(k, sample_reads, n_steps, n_warmup, reads=None):
-    """Times the reference CPU kcount on the first `sample_reads` reads of the workload. Returns (best-of-steps mean
-    k-mers/s, dict describing the run). Uses oracle/_ref/kcount_ref when present (kind "reference"), else the oracle
-    restatement (kind "port")."""
+def shm_dir():
+    return "/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir()
+
+
+def cpu_reference_run(workload, k, sample_reads, n_steps, n_warmup, reads=None, total_reads=None):
+    """Times the reference CPU kcount on the first `sample_reads` reads of the workload. Returns (mean seconds per pass,
+    counted k-mers, dict describing the run). Uses oracle/_ref/kcount_ref when present (kind "reference"), else the oracle
+    restatement (kind "port"). Only libkc_synth.so (the read generator) and oracle/ are touched: no product code."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle as O
 
-    import mhm2_kmer_analysis_v2_b200 as K
+    from mhm2_kmer_analysis_v2_b200 import reads as R
 
     if reads is None:
-        reads = K.generate(WORKLOAD, sample_reads)
+        reads = R.generate(workload, sample_reads)
     elif len(reads) > sample_reads:
         reads = reads.slice(0, sample_reads)
     occ = reads.counted_kmers(k)
     times = []
     if os.path.exists(O.REF_BIN):
         cores = min(host_cores(), 128)
-        tmpdir = "/dev/shm" if os.path.isdir("/dev/shm") else tempfile.gettempdir()
-        path = os.path.join(tmpdir, f"kc_bench_reads_{os.getpid()}.bin")
+        path = os.path.join(shm_dir(), f"kc_bench_reads_{os.getpid()}.bin")
         reads.save(path)
         try:
             for it in range(n_warmup + n_steps):
@@ -178,9 +207,19 @@ def cpu_reference_run(k, sample_reads, n_steps, n_warmup, reads=None):
         kind = "port"
         how = "oracle/kcount_oracle.c restatement, 1 thread (reference build absent)"
     mean = sum(times) / len(times)
+    # a prefix of the read stream is shallower than the full set (fewer repeats per distinct k-mer): say how much
+    cov = f"; prefix = {100.0 * len(reads) / total_reads:.1f}% of the workload's reads, i.e. that fraction of its coverage -- not like-for-like, a stated CPU baseline" if total_reads else ""
     info = {"value": occ / mean, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": f"first {len(reads)} reads of the workload ({occ} counted k-mers), {how}; {mean:.2f} s per pass"}
+            "sample": f"first {len(reads)} reads of the workload ({occ} counted k-mers), {how}; {mean:.2f} s per pass{cov}"}
     return mean, occ, info
+
+
+def spec_from_args(args, world):
+    w = WORKLOADS[args.workload]
+    k = args.k or w["k"]
+    n = args.reads_per_gpu or (w["total_reads"] // world if "total_reads" in w else w["reads_per_gpu"])
+    return dict(workload=args.workload, k=k, m=args.m, filter=int(args.filter), global_table=bool(args.global_table), reads_per_gpu=n,
+                local_bins=args.local_bins, record_bytes=args.record_bytes, table_slots=args.table_slots)
 
 
 def run_reference_arm(args):
@@ -188,12 +227,14 @@ def run_reference_arm(args):
     if rank != 0:
         return 0
     cores = min(host_cores(), 128)
-    sample = min(args.reads_per_gpu * args.gpus, args.cpu_sample_reads or 100_000 * cores)
-    mean, occ, info = cpu_reference_run(args.k, sample, args.steps, args.warmup)
+    spec = spec_from_args(args, args.gpus)
+    total = spec["reads_per_gpu"] * args.gpus
+    sample = min(total, args.cpu_sample_reads or 100_000 * cores)
+    mean, occ, info = cpu_reference_run(args.workload, spec["k"], sample, args.steps, args.warmup, total_reads=total)
     line = {
         "impl": "reference", "metric": METRIC, "value": info["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": mean * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u64", "data": "synthetic", "config": config_dict(args, args.gpus), "cpu_baseline": info,
+        "dtype": "u64", "data": "synthetic", "config": config_dict(spec, args.gpus), "cpu_baseline": info,
         "e2e": {"value": info["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -202,172 +243,320 @@ def run_reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--k", type=int, default=K_DEFAULT)
-    ap.add_argument("--reads-per-gpu", type=int, default=READS_PER_GPU)
-    ap.add_argument("--filter", type=int, default=0, help="1 = two-choice singleton filter on")
-    ap.add_argument("--local-bins", type=int, default=0)
-    ap.add_argument("--record-bytes", type=int, default=0)
-    ap.add_argument("--table-slots", type=int, default=0, help="exact table size in slots (0 = the reference's sizing rule)")
-    ap.add_argument("--global-table", action="store_true", help="count in one HBM table (kc_insert.cu) instead of bin-resident tables")
-    ap.add_argument("--e2e-steps", type=int, default=3)
-    ap.add_argument("--cpu-sample-reads", type=int, default=0)
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-lookup", action="store_true", help="skip the batched-lookup measurement against the finished result")
-    ap.add_argument("--exchange", default="pull", choices=["pull", "nccl"],
-                    help="multi-GPU: 'pull' = peers' bins mapped with CUDA IPC, the refine kernel reads them over NVLink; "
-                         "'nccl' = all-to-all of the owner regions, then refine")
-    ap.add_argument("--n-genomes", type=int, default=0, help="profiling only: fewer genomes keep the coverage of a smaller read set like the full workload's")
-    ap.add_argument("--phase-detail", action="store_true", help="also print per-phase device times to stderr")
-    args = ap.parse_args()
-    if args.warmup < 3 and args.impl == "b200":
-        print(f"note: warmup {args.warmup} < 3 (timing rules ask for >= 3)", file=sys.stderr)
+class Env:
+    """Process-wide state of the GPU arm: ranks, collectives."""
 
-    if args.impl == "reference":
-        return run_reference_arm(args)
+    def __init__(self, args):
+        import torch
 
-    import numpy as np
-    import torch
+        self.torch = torch
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world != args.gpus:
+            if self.world == 1 and args.gpus > 1:
+                raise SystemExit(f"--gpus {args.gpus} needs torchrun with {args.gpus} ranks (one process per GPU)")
+            raise SystemExit(f"WORLD_SIZE {self.world} != --gpus {args.gpus}")
+        torch.cuda.set_device(self.local_rank)
+        self.dist = None
+        self.groups = [None, None]
+        if self.world > 1:
+            import datetime
 
-    import mhm2_kmer_analysis_v2_b200 as K
-    from mhm2_kmer_analysis_v2_b200.reads import PinnedBuffer
+            import torch.distributed as dist
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            raise SystemExit(f"--gpus {args.gpus} needs torchrun with {args.gpus} ranks (one process per GPU)")
-        raise SystemExit(f"WORLD_SIZE {world} != --gpus {args.gpus}")
-    if K._lib.lib().kc_device_count() < 1:
-        raise SystemExit("bench.py: no CUDA device; the stage has no CPU path (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank), timeout=datetime.timedelta(seconds=600))
+            self.dist = dist
+            # control-plane groups of the pipelined end-to-end arm: each host thread drives its own job with its own
+            # (CPU) group, so their small all-gathers never interleave on one communicator
+            self.groups = [dist.new_group(backend="gloo", timeout=datetime.timedelta(seconds=600)) for _ in range(2)]
 
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    def barrier(self, *stages):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+        for st in stages:
+            st.sync()
+
+    def max(self, x):
+        if self.dist is None:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum(self, x):
+        if self.dist is None:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t)
+        return float(t.item())
+
+    def sum_u64(self, v):
+        """sum modulo 2^64 over the ranks (order-independent checksums)"""
+        if self.dist is None:
+            return int(v)
+        parts = [None] * self.world
+        self.dist.all_gather_object(parts, int(v))
+        return sum(parts) % (1 << 64)
+
+
+def make_stage(K, env, spec, est_kmers, **kw):
+    return K.KcountStage(spec["k"], m=spec["m"], rank=env.rank, n_ranks=env.world, device=env.local_rank, est_kmers=est_kmers,
+                         use_filter=bool(spec["filter"]), local_bins=kw.pop("local_bins", spec["local_bins"]), record_bytes=spec["record_bytes"],
+                         table_slots=spec["table_slots"], global_table=spec["global_table"], **kw)
+
+
+def one_pass(env, st, exchange, group=None):
+    """reset -> parse -> exchange -> insert -> finalize (-> release): one step of the hot path on this rank."""
     from mhm2_kmer_analysis_v2_b200.exchange import exchange_supermers, exchange_supermers_pull, release_peers
 
-    k, n = args.k, args.reads_per_gpu
-    # ---- this rank's reads, generated straight into pinned host memory
+    st.reset()
+    st.parse()
+    xb = (0, 0, 0.0)
+    if env.world > 1:
+        xb = exchange_supermers(st, group) if exchange == "nccl" else exchange_supermers_pull(st, group)
+    st.insert()
+    fin = st.finalize()
+    if env.world > 1 and exchange != "nccl":
+        release_peers(st, group)  # nobody parses again while a peer may still be reading this rank's bins
+    return fin, xb
+
+
+def parity_check(K, env, args, spec):
+    """A small seeded read set through the same path on every rank, against the CPU checker on rank 0."""
+    import numpy as np
+
+    from mhm2_kmer_analysis_v2_b200 import reads as R
+
+    k = spec["k"]
+    n_rank = max(args.parity_reads // env.world, 1000)
+    total = n_rank * env.world
+    mine = R.generate(spec["workload"], n_rank, first=env.rank * n_rank)
+    # enough fine bins that the two-level partition (parse -> refine -> count, sliced) is the path under test, as at full size
+    bins = spec["local_bins"] or (0 if (spec["filter"] or spec["global_table"]) else 131072)
+    st = make_stage(K, env, spec, est_kmers=int(np.maximum(mine.lens.astype(np.int64) - k + 1, 0).sum()), local_bins=bins)
+    if env.world > 1 and args.exchange != "nccl":
+        st.set_exchange_mode(args.exchange)
+    st.add_reads(mine)
+    for _ in range(2):  # twice: buffers, IPC mappings and layouts are reused from the second pass on
+        stats, _ = one_pass(env, st, args.exchange)
+    cs = env.sum_u64(st.checksum(False))
+    final = int(env.sum(float(stats["final_kmers"])))
+    sum_counts = int(env.sum(float(stats["sum_counts"])))
+    inserted = int(env.sum(float(stats["inserted_kmers"])))
+    fine_bins = int(stats["local_bins"])
+    st.close()
+    out = None
+    if env.rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle as O
+
+        allr = mine if env.world == 1 else R.generate(spec["workload"], total)
+        t0 = time.perf_counter()
+        if os.path.exists(O.REF_BIN):
+            path = os.path.join(shm_dir(), f"kc_parity_{os.getpid()}")
+            allr.save(path + ".reads")
+            try:
+                s = O.run_reference(path + ".reads", k, path, ranks=min(host_cores(), 32))
+                d1 = O.load_dump(path + ".d1")
+                want = (O.result_checksum(d1, False), len(d1), int(d1.counts.astype(np.uint64).sum()), int(s["occurrences"]))
+            finally:
+                for suf in (".reads", ".d1"):
+                    if os.path.exists(path + suf):
+                        os.unlink(path + suf)
+            checker = "oracle/_ref/kcount_ref (reference sources)"
+        else:
+            o = O.Oracle(k, slots_per_rank=max(4 * allr.counted_kmers(k), 1 << 16))
+            o.add_reads(allr.bytes, allr.offsets, allr.lens)
+            o.finalize()
+            fin = o.result(False)
+            want = (o.checksum(False), len(fin), int(fin.counts.astype(np.uint64).sum()), o.counted_kmers())
+            o.close()
+            checker = "oracle/libkcount_oracle.so (C restatement)"
+        got = (cs, final, sum_counts, inserted)
+        mode = "single" if env.world == 1 else args.exchange
+        out = {"reads": total, "k": k, "mode": mode, "fine_bins": fine_bins, "survivors": final, "checksum": f"{cs:016x}",
+               "checker": checker, "checker_s": round(time.perf_counter() - t0, 2), "ok": got == want}
+        if got != want:
+            out["got"], out["want"] = list(got), list(want)
+    if env.dist is not None:
+        box = [out]
+        env.dist.broadcast_object_list(box, src=0)
+        out = box[0]
+    return out
+
+
+def load_reads(K, env, spec, first=None):
+    """This rank's reads of the workload, generated straight into pinned host memory."""
+    import numpy as np
+
+    from mhm2_kmer_analysis_v2_b200.reads import PinnedBuffer
+
+    n = spec["reads_per_gpu"]
     pin_reads = PinnedBuffer(n * READ_LEN)
-    synth_kw = dict(K.CONFIGS[WORKLOAD]["synth"])
-    if args.n_genomes:
-        synth_kw["n_genomes"] = args.n_genomes
-    syn = K.Synth(**synth_kw)
+    syn = K.Synth(**dict(K.CONFIGS[spec["workload"]]["synth"], **spec.get("synth_over", {})))
     t0 = time.perf_counter()
-    reads = syn.generate(rank * n, n, out_bytes=pin_reads.array)
+    reads = syn.generate(env.rank * n if first is None else first, n, out_bytes=pin_reads.array)
     syn.close()
     pin_off, pin_len = PinnedBuffer(n * 8), PinnedBuffer(n * 2)
     pin_off.view(np.uint64, n)[:] = reads.offsets
     pin_len.view(np.uint16, n)[:] = reads.lens
+    nb = len(reads.bytes)
     reads = K.ReadSet.__new__(K.ReadSet)
-    reads.bytes, reads.offsets, reads.lens = pin_reads.array[: n * READ_LEN], pin_off.view(np.uint64, n), pin_len.view(np.uint16, n)
-    t_gen = time.perf_counter() - t0
+    reads.bytes, reads.offsets, reads.lens = pin_reads.array[:nb], pin_off.view(np.uint64, n), pin_len.view(np.uint16, n)
+    reads._pins = (pin_reads, pin_off, pin_len)
+    return reads, time.perf_counter() - t0
+
+
+def free_reads(reads):
+    pins = reads._pins
+    reads.bytes = reads.offsets = reads.lens = None
+    reads._pins = None
+    for p in pins:
+        p.free()
+
+
+def measure(K, env, args, spec, steps, warmup, headline):
+    """Device-resident arm of one configuration (+ lookups, end to end and the CPU baseline for the headline)."""
+    import numpy as np
+
+    torch = env.torch
+    k, n = spec["k"], spec["reads_per_gpu"]
+    reads, t_gen = load_reads(K, env, spec)
     occ_local = reads.counted_kmers(k)
     raw_local = int(np.maximum(reads.lens.astype(np.int64) - k + 1, 0).sum())
     h2d_bytes = len(reads.bytes) + n * 10
-
-    st = K.KcountStage(k, rank=rank, n_ranks=world, device=local_rank, est_kmers=raw_local, use_filter=bool(args.filter),
-                       local_bins=args.local_bins, record_bytes=args.record_bytes, table_slots=args.table_slots,
-                       global_table=args.global_table)
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-        st.sync()
-
-    def one_pass():
-        st.reset()
-        st.parse()
-        xb = (0, 0, 0.0)
-        if world > 1:
-            xb = exchange_supermers_pull(st) if args.exchange == "pull" else exchange_supermers(st)
-        st.insert()
-        fin = st.finalize()
-        if world > 1 and args.exchange == "pull":
-            release_peers(st)  # nobody parses again while a peer may still be reading this rank's bins
-        return fin, xb
-
-    def max_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t)
-        return float(t.item())
-
-    # ---- device-resident arm
+    st = make_stage(K, env, spec, est_kmers=raw_local)
+    if env.world > 1 and args.exchange != "nccl":
+        st.set_exchange_mode(args.exchange)
     st.add_reads(reads)
     st.sync()
-    # the clock sampler (an nvidia-smi process) starts before the warm-up: its start-up perturbs the driver for a moment,
-    # which must not fall into the timed region; the run waits for its first sample, then it samples every 200 ms through warm-up and timed steps
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
+    sampler = None
+    if headline and env.rank == 0:
+        # the clock sampler (an nvidia-smi process) starts before the warm-up: its start-up perturbs the driver for a moment,
+        # which must not fall into the timed region; it then samples every 200 ms through warm-up and timed steps
+        sampler = ClockSampler(env.local_rank)
         sampler.start()
         sampler.wait_first_sample()
-    barrier()
-    for _ in range(args.warmup):
-        stats, _ = one_pass()
+    env.barrier(st)
+    for _ in range(warmup):
+        stats, _ = one_pass(env, st, args.exchange)
+    checksum_warm = st.checksum(False)
     launches0 = st.stats()["kernel_launches"]
-    phase = {"parse": 0.0, "parse_kernel": 0.0, "insert": 0.0, "insert_kernel": 0.0, "table_clear": 0.0, "finalize": 0.0, "exchange_s": 0.0}
-    xbytes = xpulled = 0
-    barrier()
+    names = ("parse", "parse_kernel", "insert", "insert_kernel", "refine_kernel", "table_clear", "finalize", "exchange_copy")
+    phase = {nm: 0.0 for nm in names}
+    phase["exchange_s"] = 0.0
+    xbytes = 0
+    invariants = set()
+    env.barrier(st)
     st.timer_mark(0)
     step_wall = []
-    for _ in range(args.steps):
+    for _ in range(steps):
         t_s = time.perf_counter()
-        stats, xb = one_pass()
+        stats, xb = one_pass(env, st, args.exchange)
         step_wall.append((time.perf_counter() - t_s) * 1e3)  # (finalize returns the counters: every step ends synchronised)
-        for name in ("parse", "parse_kernel", "insert", "insert_kernel", "table_clear", "finalize"):
-            phase[name] += stats["ms_" + name]
+        for nm in names:
+            phase[nm] += stats["ms_" + nm]
         phase["exchange_s"] += xb[2]
         xbytes += xb[0]
-        xpulled += xb[1]
+        invariants.add((stats["final_kmers"], stats["sum_counts"], stats["unique_kmers"], stats["ge2_kmers"], stats["max_count"], stats["inserted_kmers"]))
     st.timer_mark(1)
-    barrier()
-    ms_total = st.timer_elapsed_ms(0, 1)
-    clocks = sampler.stop() if rank == 0 else None
+    env.barrier(st)
+    ms_total = env.max(st.timer_elapsed_ms(0, 1))
+    clocks = sampler.stop() if sampler else None
     launches = st.stats()["kernel_launches"] - launches0
-    ms_total = max_over_ranks(ms_total)
-    occ_all = sum_over_ranks(float(occ_local))
-    value = occ_all * args.steps / (ms_total / 1e3)
-    ms_insert_kernel = phase["insert_kernel"] / args.steps
-    inserted = stats["inserted_kmers"]  # k-mers this rank's insert launch processed
+    checksum = st.checksum(False)
+    if checksum != checksum_warm:
+        raise SystemExit(f"bench: the result changed between steps (checksum {checksum_warm:016x} -> {checksum:016x})")
+    stable = {"steps_compared": steps, "identical": len(invariants) == 1, "what": "final, sum_counts, unique, ge2, max_count, inserted of every timed step; "
+              "result checksum after the warm-up and after the last timed step"}
+    if len(invariants) != 1:
+        stable["sets_seen"] = sorted(invariants)
+        print(f"bench: WARNING: counters differ between steps: {sorted(invariants)}", file=sys.stderr)
+    occ_all = env.sum(float(occ_local))
+    value = occ_all * steps / (ms_total / 1e3)
+    ms_insert_kernel = phase["insert_kernel"] / steps
+    inserted = stats["inserted_kmers"]  # k-mers this rank's insert launches processed
+    if env.world == 1 and inserted != occ_local:
+        raise SystemExit(f"bench: {inserted} k-mers inserted, {occ_local} expected")
     peak, peak_src = load_peaks()
-    achieved = b_alg(k) * inserted / (ms_insert_kernel / 1e3) / 1e9
-    traffic = None  # DRAM bytes of one count launch, from the committed ncu --set full capture (per k-mer, scaled)
-    try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
-            tj = json.load(f)
-        if k == K_DEFAULT and not args.global_table and not args.filter:
-            traffic = tj["dram_bytes_per_counted_kmer"] * inserted
-    except Exception:
-        pass
+    achieved = b_alg(k) * inserted / (ms_insert_kernel / 1e3) / 1e9 if ms_insert_kernel > 0 else 0.0
+    hbm_table = bool(spec["filter"] or spec["global_table"])
+    per_kmer, traffic_src = profile_traffic(k, "insert" if hbm_table else "count")
     final_local = stats["final_kmers"]
-    checksum_all = None
-    if dist is not None:  # order-independent result checksum, summed over the owners (mod 2^64): the same for any exchange mode
-        cs = st.checksum(False)
-        parts = [None] * world
-        dist.all_gather_object(parts, int(cs))
-        checksum_all = sum(parts) % (1 << 64)
+    free_b, total_b = torch.cuda.mem_get_info()
+    rec = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": env.world, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+        "data": "synthetic", "config": config_dict(spec, env.world),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": per_kmer * inserted if per_kmer else None, "traffic_source": traffic_src,
+                     "kernel": "insert_kernel (HBM table)" if hbm_table else "count_kernel (bin-resident insert + purge + extension resolution)",
+                     "peak_source": peak_src, "b_alg_bytes_per_kmer": b_alg(k), "kmers_per_launch": inserted, "ms_per_launch": ms_insert_kernel,
+                     "launches_per_step": int(stats["pipeline_slices"]) if not hbm_table else int(stats["insert_kernel_launches"])},
+        "gpu_launches": int(launches), "clocks": clocks,
+        "phases_ms_per_step": {kk: (v / steps if kk != "exchange_s" else v / steps * 1e3) for kk, v in phase.items()},
+        "checksum": f"{env.sum_u64(checksum):016x}", "result_stability": stable,
+        "hbm_bytes_in_use": int(total_b - free_b),
+        "read_gen_s": t_gen, "step_wall_ms": [round(x, 2) for x in step_wall],
+    }
+    red = None
+    if env.dist is not None:
+        from mhm2_kmer_analysis_v2_b200.exchange import reduce_stats
+
+        red = reduce_stats(stats)
+    g = red or stats
+    rec["table"] = {"unique_kmers": int(g["unique_kmers"]), "final_kmers": int(g["final_kmers"]), "sum_counts": int(g["sum_counts"]),
+                    "table_bytes": int(g["table_bytes"]), "filter_bytes": int(stats["filter_bytes"]), "supermer_bytes": int(g["supermer_bytes_out"]),
+                    "local_bins": int(stats["local_bins"]), "split_passes": int(stats["split_passes"]), "result_bytes": int(stats["result_bytes"]),
+                    "insert_passes": int(stats["insert_kernel_launches"]) if hbm_table else 1}
+    if env.world > 1:
+        rec_b = stats["supermer_bytes_out"] / max(stats["supermers_out"], 1)
+        # records that crossed NVLink: what this owner consumed minus its own share (owners are balanced by the hash)
+        pulled = stats["supermers_in"] * rec_b * (env.world - 1) / env.world
+        if args.exchange == "pull":
+            xs = phase["refine_kernel"] / steps / 1e3  # the transfer happens inside the refine kernel
+            how = "pull: refine kernel reads the peers' bins over NVLink (CUDA IPC) slice by slice beside the count kernel, no staging"
+        elif args.exchange == "copy":
+            xs = phase["exchange_copy"] / steps / 1e3
+            pulled = stats["exchange_copy_bytes"]
+            how = "copy: copy engines move the peers' regions (CUDA IPC) slice by slice beside the refine / count kernels"
+        else:
+            xs = phase["exchange_s"] / steps
+            pulled = xbytes / steps
+            how = "nccl all-to-all of owner regions (slack between bins travels too), then refine + count"
+        rec["exchange"] = {"mode": how, "bytes_per_gpu_per_step": pulled, "seconds": xs,
+                           "gbps_per_gpu_per_direction": pulled / xs / 1e9 if xs > 0 else None, "nvlink_peak_gbps": 900.0,
+                           "nvlink_frac": pulled / xs / 1e9 / 900.0 if xs > 0 else None,
+                           "owner_imbalance": red.get("owner_imbalance") if red else None}
+    if not headline:
+        st.close()
+        free_reads(reads)
+        return rec
+    rec["reference_pin"] = check_full_pin(spec, env, g, rec["checksum"])
+
+    # ---- the transport north_star names literally, beside the default: same stage, NCCL all-to-all, 2 steps
+    if env.world > 1 and args.exchange != "nccl":
+        for _ in range(2):
+            one_pass(env, st, "nccl")
+        env.barrier(st)
+        st.timer_mark(2)
+        xs = 0.0
+        for _ in range(2):
+            s2, xb = one_pass(env, st, "nccl")
+            xs += xb[2]
+        st.timer_mark(3)
+        env.barrier(st)
+        ms2 = env.max(st.timer_elapsed_ms(2, 3)) / 2
+        rec["exchange_nccl"] = {"ms_per_step": ms2, "value": occ_all / (ms2 / 1e3), "all_to_all_seconds": xs / 2, "bytes_sent_per_gpu_per_step": xb[0],
+                                "gbps_per_gpu_per_direction": xb[0] / (xs / 2) / 1e9 if xs > 0 else None,
+                                "checksum": f"{env.sum_u64(st.checksum(False)):016x}"}
+        if rec["exchange_nccl"]["checksum"] != rec["checksum"]:
+            raise SystemExit("bench: the NCCL exchange produced another result than the default exchange")
+        one_pass(env, st, args.exchange)  # (the result the lookups below query)
 
     # ---- batched lookups against the device-resident result (SURVEY.md 8(f) row 1: what the next stage asks the table)
-    lookup = None
     if not args.no_lookup and final_local > 0:
         rd = st.result_device(False)
         nq = int(min(final_local, 1 << 26))
@@ -391,120 +580,235 @@ def main():
                        and torch.equal(lr[0::2], rd["right"][idx[0::2]]))
         if not hits_ok:
             raise SystemExit("bench: lookup of the result's own keys returned something else")
-        lookup = {"queries": nq, "queries_per_sec": nq / t_q, "ms_per_batch": t_q * 1e3, "index_build_ms": max(t_first - t_q, 0.0) * 1e3,
-                  "entries": int(final_local), "hit_fraction_asked": 0.5, "miss_found": int((lc[1::2] != 0).sum().item()),
-                  "where": "queries and answers resident in HBM (kc_lookup with device pointers)"}
+        rec["lookup"] = {"queries": nq, "queries_per_sec": nq / t_q, "ms_per_batch": t_q * 1e3, "index_build_ms": max(t_first - t_q, 0.0) * 1e3,
+                         "entries": int(final_local), "hit_fraction_asked": 0.5, "miss_found": int((lc[1::2] != 0).sum().item()),
+                         "where": "queries and answers resident in HBM (kc_lookup with device pointers)"}
         del q, idx, lc, ll, lr, rd
 
     # ---- end-to-end arm: host reads in, host result out, through the C ABI
-    e2e = None
     if not args.no_e2e:
-        N = st.N
-        d2h_bytes = final_local * (8 * N + 4)
-        pin_res = PinnedBuffer(max(d2h_bytes, 1) + 64)
-        res_keys = pin_res.view(np.uint64, final_local * N)
-        res_counts = pin_res.view(np.uint16, final_local, offset=final_local * N * 8)
-        res_left = pin_res.view(np.uint8, final_local, offset=final_local * (N * 8 + 2))
-        res_right = pin_res.view(np.uint8, final_local, offset=final_local * (N * 8 + 3))
-        import ctypes as C
-
-        def e2e_pass(detail=False):
-            tt = [time.perf_counter()]
-
-            def mark():
-                if detail:
-                    if detail is True:
-                        st.sync()
-                    tt.append(time.perf_counter())
-
-            st.clear_reads()
-            mark()
-            st.add_reads(reads)            # H2D from pinned memory, asynchronous on the stage's stream
-            mark()
-            s, _ = one_pass()              # with the host sink set: the survivors stream out while the count kernel runs
-            mark()
-            assert s["final_kmers"] == final_local, "result size changed between passes"
-            if detail:
-                names = ["clear_reads", "add_reads(H2D)", "parse+insert+finalize(+D2H into the sink)"]
-                print(f"e2e detail (ms, sync={detail}): " +
-                      ", ".join(f"{n} {1e3 * (b - a):.1f}" for n, a, b in zip(names, tt, tt[1:])), file=sys.stderr)
-            return s
-
-        st.set_result_sink(res_keys, res_counts, res_left, res_right)
-        for _ in range(max(2, min(args.warmup, 3))):  # warm-up: buffer pools and bin layout settle over the first two passes
-            e2e_pass()
-        if args.phase_detail:
-            e2e_pass(True)
-        barrier()
-        t0 = time.perf_counter()
-        e2e_wall = []
-        for _ in range(args.e2e_steps):
-            t_s = time.perf_counter()
-            e2e_pass("nosync" if os.environ.get("KC_E2E_TRACE") else False)
-            e2e_wall.append(round((time.perf_counter() - t_s) * 1e3, 2))  # (the pass ends synchronised: finalize returns counters)
-        barrier()
-        dt = max_over_ranks(time.perf_counter() - t0)
-        # the sink really holds the result: the counts add up to the stage's own statistic
-        got = int(res_counts[:final_local].astype(np.uint64).sum())
-        assert got == int(stats["sum_counts"]), f"result sink: counts sum {got} != {stats['sum_counts']}"
-        st.set_result_sink(None)
-        e2e = {"value": occ_all * args.e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": int(sum_over_ranks(float(h2d_bytes))),
-               "d2h_bytes_per_step": int(sum_over_ranks(float(d2h_bytes))), "steps": args.e2e_steps, "ms_per_step": dt / args.e2e_steps * 1e3, "step_wall_ms": e2e_wall,
-               "api": "kc_set_result_sink(host pinned) + kc_add_reads(host pinned) -> kc_parse [-> peer-memory pull or NCCL all-to-all] -> kc_insert -> kc_finalize (survivors land in the sink)"}
-
-    red = None
-    if dist is not None:
-        from mhm2_kmer_analysis_v2_b200.exchange import reduce_stats
-
-        red = reduce_stats(stats)
+        rec["e2e"] = e2e_arm(K, env, args, spec, st, reads, stats, occ_all, h2d_bytes, raw_local)
     # ---- CPU baseline (rank 0, single-GPU runs only)
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    st.close()
+    if env.rank == 0 and env.world == 1 and not args.no_cpu_baseline:
         cores = min(host_cores(), 128)
         sample = min(n, args.cpu_sample_reads or 100_000 * cores)
-        st.close()
-        _, _, cpu = cpu_reference_run(k, sample, 1, 0, reads=reads)
+        _, _, rec["cpu_baseline"] = cpu_reference_run(spec["workload"], k, sample, 1, 0, reads=reads, total_reads=n)
+    else:
+        rec["cpu_baseline"] = None
+    free_reads(reads)
+    return rec
 
-    if rank == 0:
-        g = red or stats
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
-            "data": "synthetic", "config": config_dict(args, world),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                         "kernel": "insert_kernel (HBM table)" if (args.filter or args.global_table) else "count_kernel (bin-resident insert + purge + extension resolution)",
-                         "peak_source": peak_src, "b_alg_bytes_per_kmer": b_alg(k),
-                         "kmers_per_launch": inserted, "ms_per_launch": ms_insert_kernel},
-            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "phases_ms_per_step": {kk: (v / args.steps if kk != "exchange_s" else v / args.steps * 1e3) for kk, v in phase.items()},
-            "table": {"unique_kmers": int(g["unique_kmers"]), "final_kmers": int(g["final_kmers"]), "sum_counts": int(g["sum_counts"]),
-                      "table_bytes": int(g["table_bytes"]), "supermer_bytes": int(g["supermer_bytes_out"]),
-                      "local_bins": int(stats["local_bins"]), "split_passes": int(stats["split_passes"]),
-                      "result_bytes": int(stats["result_bytes"])},
-            "read_gen_s": t_gen, "lookup": lookup, "step_wall_ms": [round(x, 2) for x in step_wall],
-        }
-        if world > 1:
-            xs = phase["exchange_s"] / args.steps
-            if args.exchange == "pull":
-                # the transfer happens inside the refine kernel: time = insert phase minus the count kernel
-                xs = (phase["insert"] - phase["insert_kernel"]) / args.steps / 1e3
-                rec_b = stats["supermer_bytes_out"] / max(stats["supermers_out"], 1)
-                # records that crossed NVLink: what this owner consumed minus its own share (owners are balanced by the hash)
-                xpulled = stats["supermers_in"] * rec_b * (world - 1) / world * args.steps
-                line["exchange"] = {"mode": "pull: refine kernel reads the peers' bins over NVLink (CUDA IPC), no staging",
-                                    "bytes_pulled_per_gpu_per_step_approx": xpulled / args.steps, "seconds_refine_incl_local_bins": xs,
-                                    "gbps_per_gpu_per_direction": (xpulled / args.steps) / xs / 1e9 if xs > 0 else None,
-                                    "nvlink_peak_gbps": 900.0, "owner_imbalance": red.get("owner_imbalance") if red else None}
-            else:
-                line["exchange"] = {"mode": "nccl all-to-all of owner regions (slack between bins travels too)",
-                                    "bytes_sent_per_gpu_per_step": xbytes / args.steps, "seconds": xs,
-                                    "gbps_per_gpu_per_direction": (xbytes / args.steps) / xs / 1e9 if xs > 0 else None,
-                                    "nvlink_peak_gbps": 900.0, "owner_imbalance": red.get("owner_imbalance") if red else None}
-            line["table"]["checksum_sum_over_ranks"] = checksum_all
+
+def check_full_pin(spec, env, g, checksum):
+    """The reference's own result for this exact configuration, when tests/golden/full_config_pins.json holds one
+    (tools/pin_full_config.py ran oracle/_ref/kcount_ref on all reads of the workload)."""
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "full_config_pins.json")) as f:
+            pins = json.load(f)["pins"]
+    except Exception:
+        return None
+    for p in pins:
+        if (p["workload"], p["k"], p["n_reads"]) == (spec["workload"], spec["k"], spec["reads_per_gpu"] * env.world) and not spec.get("synth_over"):
+            got = {"entries": int(g["unique_kmers"]), "survivors": int(g["final_kmers"]), "sum_count": int(g["sum_counts"]), "checksum_d1": checksum}
+            want = {kk: p[kk] for kk in got}
+            if spec["filter"]:
+                got.pop("entries"), want.pop("entries")
+            ok = got == want
+            if not ok:
+                print(f"bench: result differs from the reference pin: {got} != {want}", file=sys.stderr)
+            return {"ok": ok, "source": "tests/golden/full_config_pins.json: oracle/_ref/kcount_ref (reference sources) on all reads of this configuration",
+                    "reads": p["n_reads"], "survivors": p["survivors"]}
+    return None
+
+
+def e2e_arm(K, env, args, spec, st0, reads, stats, occ_all, h2d_bytes, raw_local):
+    import numpy as np
+
+    from mhm2_kmer_analysis_v2_b200.reads import PinnedBuffer
+
+    depth = max(1, min(args.e2e_depth, 2))
+    if env.world > 1 and args.exchange == "nccl":
+        depth = 1  # the data all-to-all runs on the one NCCL communicator: one job at a time
+    groups = env.groups if not (env.world > 1 and args.exchange == "nccl") else [None, None]
+    final_local = stats["final_kmers"]
+    N = st0.N
+    d2h_bytes = final_local * (8 * N + 4)
+    stages = [st0]
+    if depth == 2:
+        st1 = make_stage(K, env, spec, est_kmers=raw_local)
+        if env.world > 1 and args.exchange != "nccl":
+            st1.set_exchange_mode(args.exchange)
+        stages.append(st1)
+    sinks = []
+    for st in stages:
+        pin = PinnedBuffer(max(d2h_bytes, 1) + 64)
+        keys = pin.view(np.uint64, final_local * N)
+        counts = pin.view(np.uint16, final_local, offset=final_local * N * 8)
+        left = pin.view(np.uint8, final_local, offset=final_local * (N * 8 + 2))
+        right = pin.view(np.uint8, final_local, offset=final_local * (N * 8 + 3))
+        st.set_result_sink(keys, counts, left, right)
+        sinks.append((pin, keys, counts, left, right))
+    errors = []
+
+    def job(t, n_pass, walls):
+        try:
+            torch = env.torch
+            torch.cuda.set_device(env.local_rank)
+            st = stages[t]
+            for _ in range(n_pass):
+                t_s = time.perf_counter()
+                st.clear_reads()
+                st.add_reads(reads)  # H2D from pinned memory, asynchronous on the stage's input stream
+                s, _ = one_pass(env, st, args.exchange, groups[t])  # the survivors stream into the sink while the count kernel runs
+                if s["final_kmers"] != final_local:
+                    raise RuntimeError("result size changed between passes")
+                walls.append(round((time.perf_counter() - t_s) * 1e3, 2))
+        except BaseException as e:  # noqa: BLE001 -- re-raised on the main thread
+            errors.append(e)
+
+    def run(n_each):
+        walls = [[] for _ in stages]
+        ths = [threading.Thread(target=job, args=(t, n_each, walls[t])) for t in range(len(stages))]
+        t0 = time.perf_counter()
+        for th in ths:
+            th.start()
+        for th in ths:
+            th.join()
+        if errors:
+            raise errors[0]
+        return time.perf_counter() - t0, walls
+
+    run(2)  # warm-up: buffer pools and bin layouts settle over the first two passes of every stage
+    n_each = max(args.e2e_steps // depth, 1)
+    env.barrier(*stages)
+    dt, walls = run(n_each)
+    env.barrier(*stages)
+    dt = env.max(dt)
+    n_jobs = n_each * depth
+    # the sinks really hold the result: the counts add up to the stage's own statistic
+    for (_, _, counts, _, _) in sinks:
+        got = int(counts[:final_local].astype(np.uint64).sum())
+        assert got == int(stats["sum_counts"]), f"result sink: counts sum {got} != {stats['sum_counts']}"
+    for st in stages:
+        st.set_result_sink(None)
+    for st in stages[1:]:
+        st.close()
+    h2d_all, d2h_all = env.sum(float(h2d_bytes)), env.sum(float(d2h_bytes))
+    ms = dt / n_jobs * 1e3
+    out = {"value": occ_all * n_jobs / dt, "unit": UNIT, "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),
+           "steps": n_jobs, "ms_per_step": ms, "jobs_in_flight": depth, "job_wall_ms": walls,
+           "pcie_gbps_per_gpu": {"h2d": h2d_bytes / (ms / 1e3) / 1e9, "d2h": d2h_bytes / (ms / 1e3) / 1e9},
+           "api": "kc_set_result_sink(host pinned) + kc_add_reads(host pinned) -> kc_parse [-> exchange] -> kc_insert -> kc_finalize (survivors land in the "
+                  "sink)" + ("; two stage objects driven by two host threads, so one job's input copy overlaps the other's result copy" if depth == 2 else "")}
+    for s in sinks:
+        s[0].free()
+    return out
+
+
+def sub_config_specs(args, world):
+    """(label, spec overrides) of the other BASELINE configs this run can hold."""
+    base = dict(m=0, filter=0, global_table=False, local_bins=0, record_bytes=0, table_slots=0)
+    out = []
+
+    def add(label, workload, k, **kw):
+        w = WORKLOADS[workload]
+        n = kw.pop("reads_per_gpu", None) or (w["total_reads"] // world if "total_reads" in w else w["reads_per_gpu"])
+        out.append((label, dict(base, workload=workload, k=k, reads_per_gpu=n, **kw)))
+
+    if world == 1:
+        add("C1_k21", "C1", 21)
+        add("C2_k21", "C2", 21)
+        add("C2_k55", "C2", 55)
+    if world in (1, 2, 4, 8):
+        for k in (77, 99):
+            add(f"C4_k{k}_m15", "C4", k, m=15)
+            add(f"C4_k{k}_m27", "C4", k, m=27)
+    if world == 1:
+        add("C5_k21_filter_off_resident", "C5", 21)
+        add("C5_k21_filter_off_hbm_table", "C5", 21, global_table=True)
+        add("C5_k21_filter_on", "C5", 21, filter=1)
+    if world == 8 or args.configs == "all":
+        for k in (21, 33, 55):
+            add(f"C3_k{k}", "C3", k)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
+    ap.add_argument("--k", type=int, default=0, help="0 = the workload's k")
+    ap.add_argument("--m", type=int, default=0, help="minimizer length; 0 = the reference rule clamp(2k/3+1, 15, 27)")
+    ap.add_argument("--reads-per-gpu", type=int, default=0, help="0 = the workload's size")
+    ap.add_argument("--filter", type=int, default=0, help="1 = two-choice singleton filter on")
+    ap.add_argument("--local-bins", type=int, default=0)
+    ap.add_argument("--record-bytes", type=int, default=0)
+    ap.add_argument("--table-slots", type=int, default=0, help="exact table size in slots (0 = the reference's sizing rule)")
+    ap.add_argument("--global-table", action="store_true", help="count in one HBM table (kc_insert.cu) instead of bin-resident tables")
+    ap.add_argument("--e2e-steps", type=int, default=4)
+    ap.add_argument("--e2e-depth", type=int, default=2, help="jobs in flight in the end-to-end arm (1 = strictly serial)")
+    ap.add_argument("--cpu-sample-reads", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-lookup", action="store_true", help="skip the batched-lookup measurement against the finished result")
+    ap.add_argument("--no-parity", action="store_true", help="skip the untimed parity pass against the CPU checker")
+    ap.add_argument("--parity-reads", type=int, default=400_000, help="reads (all ranks together) of the parity pass")
+    ap.add_argument("--configs", default="auto", choices=["none", "auto", "all"], help="also measure the other BASELINE configs (reduced steps)")
+    ap.add_argument("--exchange", default="pull", choices=["pull", "copy", "nccl"],
+                    help="multi-GPU: 'pull' = peers' bins mapped with CUDA IPC, the refine kernel reads them over NVLink; 'copy' = copy "
+                         "engines move them slice by slice; 'nccl' = all-to-all of the owner regions, then refine")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        print(f"note: warmup {args.warmup} < 3 (timing rules ask for >= 3)", file=sys.stderr)
+
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import mhm2_kmer_analysis_v2_b200 as K
+
+    if K._lib.lib().kc_device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device; the stage has no CPU path (use --impl reference for the CPU arm)")
+    env = Env(args)
+    spec = spec_from_args(args, env.world)
+
+    parity = None
+    if not args.no_parity:
+        parity = parity_check(K, env, args, spec)
+        if not parity["ok"]:
+            if env.rank == 0:
+                print(json.dumps({"parity_check": parity}), flush=True)
+            raise SystemExit("bench: parity check against the CPU checker FAILED")
+
+    line = measure(K, env, args, spec, args.steps, args.warmup, headline=True)
+    line["parity_check"] = parity
+    if args.configs != "none":
+        cfgs = {}
+        for label, sp in sub_config_specs(args, env.world):
+            try:
+                r = measure(K, env, args, sp, 2, 2, headline=False)
+                cfgs[label] = {"value": r["value"], "ms_per_step": r["ms_per_step"], "k": sp["k"], "m": sp["m"] or None, "filter": bool(sp["filter"]),
+                               "global_table": bool(sp["global_table"]), "reads_per_gpu": sp["reads_per_gpu"], "steps": 2, "warmup": 2,
+                               "phases_ms_per_step": r["phases_ms_per_step"], "roofline_frac": r["roofline"]["frac"],
+                               "roofline_kernel": r["roofline"]["kernel"], "b_alg_bytes_per_kmer": r["roofline"]["b_alg_bytes_per_kmer"],
+                               "split_passes": r["table"]["split_passes"], "local_bins": r["table"]["local_bins"],
+                               "unique_kmers": r["table"]["unique_kmers"], "final_kmers": r["table"]["final_kmers"],
+                               "table_bytes": r["table"]["table_bytes"], "filter_bytes": r["table"]["filter_bytes"],
+                               "insert_passes": r["table"]["insert_passes"], "hbm_bytes_in_use": r["hbm_bytes_in_use"], "checksum": r["checksum"],
+                               "exchange": r.get("exchange")}
+            except SystemExit:
+                raise
+            except Exception as e:  # noqa: BLE001 -- a sub-config must not take the headline down; the failure is reported
+                cfgs[label] = {"error": str(e)[:300]}
+        line["configs"] = cfgs
+    if env.rank == 0:
         print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    if env.dist is not None:
+        env.dist.barrier()
+        env.dist.destroy_process_group()
     return 0
 
 

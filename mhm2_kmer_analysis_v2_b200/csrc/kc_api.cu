@@ -234,7 +234,9 @@ static void configure_bins(kc_ctx *c) {
         P = 8192;  // no rank-independent estimate: a fixed count keeps the ranks' headers compatible; big bins are split
       } else {
         const double distinct = (double)est / depth + (double)est * kmer_err;
-        const double per_bin = 0.6 * count_table_slots(c->N, R_multi, c->k);
+        double load = 0.6;
+        if (const char *e = getenv("KC_BIN_LOAD")) load = std::min(std::max(atof(e), 0.1), 2.0);  // (experiments)
+        const double per_bin = load * count_table_slots(c->N, R_multi, c->k);
         P = (uint32_t)std::min<double>(std::ceil(distinct / per_bin), (double)(1u << 26));
         if (P < 1) P = 1;
       }
@@ -1121,7 +1123,24 @@ static int fine_header_bytes(const kc_ctx *c) {
 // so the NVLink transfer (DMA, no SMs), the HBM-bound refine pass and the issue-bound count pass of neighbouring slices
 // overlap. Sizes the host needs (d_fine, grid shapes) come from bounds it already has: the parse-side record counts and
 // the region sizes the exchange reported.
-static int n_pipeline_slices(const kc_ctx *c) { return (uint32_t)c->P >= 64u * kSlices ? kSlices : 1; }
+static int n_pipeline_slices(const kc_ctx *c) {
+  int S = (uint32_t)c->P >= 64u * kSlices ? kSlices : 1;
+  // one rank and no result sink: nothing to overlap with, and every slice boundary costs the count kernel a tail
+  if (c->G == 1 && !c->sink_keys) S = 1;
+  if (const char *e = getenv("KC_SLICES")) {  // (experiments)
+    const int v = atoi(e);
+    if (v >= 1 && v <= kSlices && (uint32_t)c->P >= 64u * (uint32_t)v) S = v;
+  }
+  return S;
+}
+// Refine slice i + 1 beside count slice i (separate streams)? Measured on one GPU (C2): the two kernels cannot share an SM
+// (the count CTAs hold all of its shared memory), so refine CTAs displace count CTAs and the pair takes 57.0 ms against
+// 51.7 ms back to back. With peers the refine kernel spends its time waiting for NVLink, and hiding that behind the count
+// pass wins.
+static bool refine_overlaps_count(const kc_ctx *c) {
+  if (const char *e = getenv("KC_REFINE_OVERLAP")) return atoi(e) != 0;  // (experiments)
+  return c->G > 1 && c->xmode == KC_XCHG_PULL;
+}
 
 // upper bound of the records this owner will consume (exact for one rank)
 static uint64_t record_bound(const kc_ctx *c) {
@@ -1221,6 +1240,7 @@ static int launch_count_pipeline(kc_ctx *c, bool redo) {
   c->xfer_bytes = 0;
   for (auto &x : c->xfer_started) x = false;
   const bool to_sink = !redo && c->sink_keys && S > 1;
+  cudaStream_t rs = refine_overlaps_count(c) ? c->refine_stream : c->stream;
 
   RefineParams rp;
   memset(&rp, 0, sizeof rp);
@@ -1246,10 +1266,10 @@ static int launch_count_pipeline(kc_ctx *c, bool redo) {
     rp.dst = c->d_fine;
     avg_records = record_bound(c) / std::max<uint64_t>(rp.n_coarse, 1);
     if (copy) {
-      int rc = queue_peer_copies(c, -1, S, c->refine_stream);  // the peers' header blocks
+      int rc = queue_peer_copies(c, -1, S, rs);  // the peers' header blocks
       if (rc) return rc;
     }
-    CK(launch_refine_totals(rp, c->refine_stream, &c->launches));
+    CK(launch_refine_totals(rp, rs, &c->launches));
   } else if (copy) {
     // no refine pass: the count kernel reads every source's segments itself -- everything has to be here first
     int rc = queue_peer_copies(c, -1, S, c->stream);
@@ -1260,16 +1280,16 @@ static int launch_count_pipeline(kc_ctx *c, bool redo) {
     const uint32_t c0 = slice_edge((uint32_t)c->P, i, S), c1 = slice_edge((uint32_t)c->P, i + 1, S);
     if (refine && !redo) {
       if (copy) {
-        int rc = queue_peer_copies(c, i, S, c->refine_stream);
+        int rc = queue_peer_copies(c, i, S, rs);
         if (rc) return rc;
       }
       rp.coarse_begin = c0;
       rp.coarse_end = c1;
-      CK(cudaEventRecord(c->ev_rs0[i], c->refine_stream));
-      CK(launch_refine(rp, avg_records, c->sm_count, c->refine_stream, &c->launches));
-      CK(cudaEventRecord(c->ev_rs1[i], c->refine_stream));
+      CK(cudaEventRecord(c->ev_rs0[i], rs));
+      CK(launch_refine(rp, avg_records, c->sm_count, rs, &c->launches));
+      CK(cudaEventRecord(c->ev_rs1[i], rs));
       c->n_refine_slices = i + 1;
-      CK(cudaStreamWaitEvent(c->stream, c->ev_rs1[i], 0));
+      if (rs != c->stream) CK(cudaStreamWaitEvent(c->stream, c->ev_rs1[i], 0));
     }
     cp.bin_begin = c0 << c->fine_shift;
     cp.bin_end = c1 << c->fine_shift;
