@@ -236,7 +236,17 @@ static void configure_bins(kc_ctx *c) {
         const double distinct = (double)est / depth + (double)est * kmer_err;
         double load = 0.6;
         if (const char *e = getenv("KC_BIN_LOAD")) load = std::min(std::max(atof(e), 0.1), 2.0);  // (experiments)
-        const double per_bin = load * count_table_slots(c->N, R_multi, c->k);
+        const double slots = count_table_slots(c->N, R_multi, c->k);
+        double per_bin = load * slots;
+        // k-mers arrive in a bin in GROUPS (all k-mers of a minimizer instance, ~(k - m + 2) / 2 of them): with long windows a
+        // bin holds few, big groups and its population scatters widely around the mean -- measured on C4 (k = 77 / 99): a third
+        // of the bins overflowed their table and were split, i.e. walked three times. Keep mu + 3 sqrt(g mu) under the claim
+        // limit (0.85 slots); the factor 1.25 is the reference estimate's own margin over what the data shows.
+        if (!getenv("KC_BIN_LOAD")) {
+          const double g = std::max(1.0, (c->k - c->m + 2) / 2.0), lim = 0.85 * slots, z = 3.0;
+          const double x = (-z * std::sqrt(g) + std::sqrt(z * z * g + 4.0 * lim)) / 2.0;  // sqrt(mu): x^2 + z sqrt(g) x - lim = 0
+          per_bin = std::min(per_bin, 1.25 * x * x);
+        }
         P = (uint32_t)std::min<double>(std::ceil(distinct / per_bin), (double)(1u << 26));
         if (P < 1) P = 1;
       }
@@ -254,6 +264,7 @@ static void configure_bins(kc_ctx *c) {
   uint32_t fine_shift = 0;
   if (c->resident && P >= 65536u) {
     fine_shift = c->G >= 4 ? 6 : (c->G >= 2 ? 5 : 4);
+    while (fine_shift < 6 && (uint64_t)(P >> fine_shift) * c->G > 700000u) fine_shift++;  // (long k: many small fine bins)
     if (const char *e = getenv("KC_FINE_SHIFT")) fine_shift = (uint32_t)std::min(std::max(atoi(e), 1), 6);  // (experiments)
     P = (P + (1u << fine_shift) - 1u) >> fine_shift;
   }

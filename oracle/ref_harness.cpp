@@ -39,8 +39,15 @@ char comp_nucleotide(char ch) {
   return 0;
 }
 
+#ifdef KC_B200_GLUE
+// the same driver over the B200 binding: integration/kcount_b200_glue.cpp takes the place of kcount_cpu.cpp at the
+// reference's link-time plug point (src/kcount/CMakeLists.txt:24-69) -> oracle/_ref/kcount_ref_b200
+#define KCOUNT_B200_SHIM_WORLD
+#include "../integration/kcount_b200_glue.cpp"
+#else
 #include "kcount/kcount_cpu.cpp"  // pulls kcount.hpp / kmer_dht.hpp / kmer.hpp; instantiates both inserters
 #undef SLOG_CPU_HT
+#endif
 
 // ---------------------------------------------------------------- reads file (format: see reads_io.h)
 #include "reads_io.h"
@@ -136,6 +143,11 @@ static void run_rank(const Args &a, const kc_reads_file &rf, RankResult *res) {
     res->sum_count = sum;
     if (!a.out.empty()) write_part<MAX_K>(a.out + ".d1.rank" + std::to_string(w.rank), keys, vals, 3);
   }
+#ifdef KC_B200_GLUE
+  res->n_ext = 0;
+  res->sum_all_counts = res->n_entries = res->max_count = 0;
+  (void)a.extended;
+#else
   // --- D2: every table entry with count >= 2, with its 8 saturating ext counters and the chosen
   //     ext chars (incl. X / F). Reads the file-local KmerMapExts through -fno-access-control.
   {
@@ -171,6 +183,7 @@ static void run_rank(const Args &a, const kc_reads_file &rf, RankResult *res) {
     res->max_count = max_count;
     if (a.extended && !a.out.empty()) write_part<MAX_K>(a.out + ".d2.rank" + std::to_string(w.rank), keys, vals, 11);
   }
+#endif
 }
 
 static void merge_parts(const std::string &out, const char *tag, int P) {
@@ -293,10 +306,15 @@ int main(int argc, char **argv) {
   }
   if (!a.out.empty()) {
     merge_parts(a.out, "d1", P);
+#ifndef KC_B200_GLUE
     if (a.extended) merge_parts(a.out, "d2", P);
+#endif
   }
   // without u16 saturation, sum of all table counts == counted occurrences iff nothing was dropped
   long long dropped = t.max_count < 65535 ? (long long)t.occurrences - (long long)t.sum_all_counts : -1;
+#ifdef KC_B200_GLUE
+  dropped = -1;  // (the binding fails loudly instead of dropping: KC_ERR_TABLE_FULL)
+#endif
   printf(
       "{\"k\": %u, \"ranks\": %d, \"reads\": %llu, \"occurrences\": %llu, \"t_dht_s\": %.6f, \"t_analyze_s\": %.6f, "
       "\"entries\": %llu, \"final_kmers\": %llu, \"ge2_kmers\": %llu, \"sum_count\": %llu, \"max_count\": %llu, "

@@ -28,6 +28,8 @@ struct World {
   int nranks = 1;
   Shared *sh = nullptr;
   Mailbox *boxes = nullptr;  // [src * nranks + dst], in shared memory
+  unsigned char *gather = nullptr;  // [nranks * kGatherBytes]: all-gather of small records (the B200 glue's IPC handles)
+  static constexpr size_t kGatherBytes = 2048;
   int local_sense = 0;
 
   static void *shared_alloc(size_t bytes) {
@@ -46,6 +48,7 @@ struct World {
     new (sh) Shared();
     sh->bar_count = 0;
     sh->bar_sense = 0;
+    gather = (unsigned char *)shared_alloc(kGatherBytes * P);
     boxes = (Mailbox *)shared_alloc(sizeof(Mailbox) * P * P);
     for (int i = 0; i < P * P; i++) {
       new (&boxes[i]) Mailbox();
@@ -80,6 +83,22 @@ struct World {
     }
     barrier();
     return acc;
+  }
+
+  // every rank contributes `bytes` bytes; all[r * bytes ...] = rank r's record
+  void allgather_bytes(const void *mine, size_t bytes, void *all) {
+    if (bytes > kGatherBytes) {
+      fprintf(stderr, "shim allgather: record of %zu bytes\n", bytes);
+      abort();
+    }
+    if (nranks == 1) {
+      memcpy(all, mine, bytes);
+      return;
+    }
+    memcpy(gather + (size_t)rank * kGatherBytes, mine, bytes);
+    barrier();
+    for (int r = 0; r < nranks; r++) memcpy((unsigned char *)all + (size_t)r * bytes, gather + (size_t)r * kGatherBytes, bytes);
+    barrier();
   }
 
   void post(int dst, const void *bytes, uint64_t n) {
