@@ -323,14 +323,56 @@ def one_pass(env, st, exchange, group=None):
     return fin, xb
 
 
-def parity_check(K, env, args, spec):
-    """A small seeded read set through the same path on every rank, against the CPU checker on rank 0."""
+def parity_reads_per_rank(args, world):
+    return max(args.parity_reads // world, 1000)
+
+
+def parity_reference(args, spec, world):
+    """The CPU checker's answer for the parity pass: (checksum of D1, survivors, sum of counts, counted k-mers). Runs on rank 0
+    BEFORE torch / CUDA are initialised: it forks (oracle/_ref/kcount_ref, one rank per host core) and churns host memory,
+    neither of which should happen next to a live CUDA context that is about to be timed."""
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+
+    from mhm2_kmer_analysis_v2_b200 import reads as R
+
+    k = spec["k"]
+    total = parity_reads_per_rank(args, world) * world
+    allr = R.generate(spec["workload"], total)
+    t0 = time.perf_counter()
+    if os.path.exists(O.REF_BIN):
+        path = os.path.join(shm_dir(), f"kc_parity_{os.getpid()}")
+        allr.save(path + ".reads")
+        try:
+            s = O.run_reference(path + ".reads", k, path, ranks=min(host_cores(), 32))
+            d1 = O.load_dump(path + ".d1")
+            want = (O.result_checksum(d1, False), len(d1), int(d1.counts.astype(np.uint64).sum()), int(s["occurrences"]))
+        finally:
+            for suf in (".reads", ".d1"):
+                if os.path.exists(path + suf):
+                    os.unlink(path + suf)
+        checker = "oracle/_ref/kcount_ref (reference sources)"
+    else:
+        o = O.Oracle(k, slots_per_rank=max(4 * allr.counted_kmers(k), 1 << 16))
+        o.add_reads(allr.bytes, allr.offsets, allr.lens)
+        o.finalize()
+        fin = o.result(False)
+        want = (o.checksum(False), len(fin), int(fin.counts.astype(np.uint64).sum()), o.counted_kmers())
+        o.close()
+        checker = "oracle/libkcount_oracle.so (C restatement)"
+    return {"want": want, "checker": checker, "checker_s": round(time.perf_counter() - t0, 2)}
+
+
+def parity_check(K, env, args, spec, ref):
+    """A small seeded read set through the same path on every rank, against the CPU checker's answer (rank 0 holds it)."""
     import numpy as np
 
     from mhm2_kmer_analysis_v2_b200 import reads as R
 
     k = spec["k"]
-    n_rank = max(args.parity_reads // env.world, 1000)
+    n_rank = parity_reads_per_rank(args, env.world)
     total = n_rank * env.world
     mine = R.generate(spec["workload"], n_rank, first=env.rank * n_rank)
     # enough fine bins that the two-level partition (parse -> refine -> count, sliced) is the path under test, as at full size
@@ -347,37 +389,13 @@ def parity_check(K, env, args, spec):
     inserted = int(env.sum(float(stats["inserted_kmers"])))
     fine_bins = int(stats["local_bins"])
     st.close()
+    del mine
     out = None
     if env.rank == 0:
-        sys.path.insert(0, os.path.join(ROOT, "oracle"))
-        import oracle as O
-
-        allr = mine if env.world == 1 else R.generate(spec["workload"], total)
-        t0 = time.perf_counter()
-        if os.path.exists(O.REF_BIN):
-            path = os.path.join(shm_dir(), f"kc_parity_{os.getpid()}")
-            allr.save(path + ".reads")
-            try:
-                s = O.run_reference(path + ".reads", k, path, ranks=min(host_cores(), 32))
-                d1 = O.load_dump(path + ".d1")
-                want = (O.result_checksum(d1, False), len(d1), int(d1.counts.astype(np.uint64).sum()), int(s["occurrences"]))
-            finally:
-                for suf in (".reads", ".d1"):
-                    if os.path.exists(path + suf):
-                        os.unlink(path + suf)
-            checker = "oracle/_ref/kcount_ref (reference sources)"
-        else:
-            o = O.Oracle(k, slots_per_rank=max(4 * allr.counted_kmers(k), 1 << 16))
-            o.add_reads(allr.bytes, allr.offsets, allr.lens)
-            o.finalize()
-            fin = o.result(False)
-            want = (o.checksum(False), len(fin), int(fin.counts.astype(np.uint64).sum()), o.counted_kmers())
-            o.close()
-            checker = "oracle/libkcount_oracle.so (C restatement)"
-        got = (cs, final, sum_counts, inserted)
+        got, want = (cs, final, sum_counts, inserted), tuple(ref["want"])
         mode = "single" if env.world == 1 else args.exchange
         out = {"reads": total, "k": k, "mode": mode, "fine_bins": fine_bins, "survivors": final, "checksum": f"{cs:016x}",
-               "checker": checker, "checker_s": round(time.perf_counter() - t0, 2), "ok": got == want}
+               "checker": ref["checker"], "checker_s": ref["checker_s"], "ok": got == want}
         if got != want:
             out["got"], out["want"] = list(got), list(want)
     if env.dist is not None:
@@ -693,6 +711,29 @@ def e2e_arm(K, env, args, spec, st0, reads, stats, occ_all, h2d_bytes, raw_local
     for (_, _, counts, _, _) in sinks:
         got = int(counts[:final_local].astype(np.uint64).sum())
         assert got == int(stats["sum_counts"]), f"result sink: counts sum {got} != {stats['sum_counts']}"
+    # ---- the same pass starting from the reference's real in-memory reads: 16-byte PackedRead headers
+    # pointing into 4 MB allocator blocks -> kc_add_packed_reads (host threads gather into pinned staging, piece by piece)
+    packed = None
+    if env.world == 1 and not args.no_packed:
+        layout = K.PackedReadsLayout(reads)
+        st = stages[0]
+        t_add, t_all = [], []
+        for it in range(3):
+            t_s = time.perf_counter()
+            st.clear_reads()
+            st.add_packed_reads(layout)
+            t_a = time.perf_counter()
+            s, _ = one_pass(env, st, args.exchange, groups[0])
+            t_e = time.perf_counter()
+            if s["final_kmers"] != final_local or s["sum_counts"] != stats["sum_counts"]:
+                raise RuntimeError("kc_add_packed_reads: another result than kc_add_reads")
+            if it:
+                t_add.append((t_a - t_s) * 1e3), t_all.append((t_e - t_s) * 1e3)
+        packed = {"ms_per_step": sum(t_all) / len(t_all), "ms_add_packed_reads": sum(t_add) / len(t_add), "allocator_blocks": layout.n_blocks,
+                  "value": occ_all / (sum(t_all) / len(t_all) / 1e3), "jobs_in_flight": 1,
+                  "what": "kc_add_packed_reads(vector<PackedRead> headers -> 4 MB blocks, pageable host memory) -> parse -> insert -> finalize into the pinned "
+                          "sink; the gather of the bytes into pinned staging by host threads is inside the time"}
+        del layout
     for st in stages:
         st.set_result_sink(None)
     for st in stages[1:]:
@@ -702,6 +743,7 @@ def e2e_arm(K, env, args, spec, st0, reads, stats, occ_all, h2d_bytes, raw_local
     out = {"value": occ_all * n_jobs / dt, "unit": UNIT, "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),
            "steps": n_jobs, "ms_per_step": ms, "jobs_in_flight": depth, "job_wall_ms": walls,
            "pcie_gbps_per_gpu": {"h2d": h2d_bytes / (ms / 1e3) / 1e9, "d2h": d2h_bytes / (ms / 1e3) / 1e9},
+           "from_packed_reads_container": packed,
            "api": "kc_set_result_sink(host pinned) + kc_add_reads(host pinned) -> kc_parse [-> exchange] -> kc_insert -> kc_finalize (survivors land in the "
                   "sink)" + ("; two stage objects driven by two host threads, so one job's input copy overlaps the other's result copy" if depth == 2 else "")}
     for s in sinks:
@@ -757,6 +799,7 @@ def main():
     ap.add_argument("--cpu-sample-reads", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-packed", action="store_true", help="skip the end-to-end pass that starts from the reference's PackedReads memory layout")
     ap.add_argument("--no-lookup", action="store_true", help="skip the batched-lookup measurement against the finished result")
     ap.add_argument("--no-parity", action="store_true", help="skip the untimed parity pass against the CPU checker")
     ap.add_argument("--parity-reads", type=int, default=400_000, help="reads (all ranks together) of the parity pass")
@@ -771,6 +814,11 @@ def main():
     if args.impl == "reference":
         return run_reference_arm(args)
 
+    world0 = int(os.environ.get("WORLD_SIZE", "1"))
+    ref = None
+    if not args.no_parity and int(os.environ.get("RANK", "0")) == 0:
+        ref = parity_reference(args, spec_from_args(args, world0), world0)  # before any CUDA context exists in this process
+
     import mhm2_kmer_analysis_v2_b200 as K
 
     if K._lib.lib().kc_device_count() < 1:
@@ -780,7 +828,7 @@ def main():
 
     parity = None
     if not args.no_parity:
-        parity = parity_check(K, env, args, spec)
+        parity = parity_check(K, env, args, spec, ref)
         if not parity["ok"]:
             if env.rank == 0:
                 print(json.dumps({"parity_check": parity}), flush=True)

@@ -42,6 +42,12 @@ int kc_synth_generate(const kc_synth *s, uint64_t first, uint64_t n, uint8_t *by
                       uint64_t *n_bytes, int n_threads);
 int kc_reads_save(const char *path, const uint8_t *bytes, uint64_t n_bytes, const uint64_t *offsets, const uint16_t *lens,
                   uint64_t n_reads);
+/* A read set in the reference's PackedReads memory layout (src/packed_reads.hpp:68-79, 136): headers[2 i] = bit fields
+ * {is_allocated : 1, read_id : 47, read_len : 16}, headers[2 i + 1] = pointer to the read's bytes inside `arena`, which is
+ * cut into blocks of block_bytes (4 MB in the reference) filled by a bump allocator, placed in descending address order.
+ * Input of kc_add_packed_reads in tests and bench. Returns 0, -1 (argument) or -3 (arena too small). */
+int kc_reads_to_packed_layout(const uint8_t *bytes, const uint64_t *offsets, const uint16_t *lens, uint64_t n_reads, uint8_t *arena,
+                              uint64_t arena_bytes, uint64_t block_bytes, uint64_t *headers, uint64_t *blocks_used);
 
 #ifdef __cplusplus
 }

@@ -143,6 +143,14 @@ int kc_device_count(void);
  * on the context's input stream when pinned/device) and may be released or overwritten after kc_sync(). */
 int kc_add_reads(kc_ctx *ctx, const uint8_t *bytes, uint64_t n_bytes, const uint64_t *offsets, const uint16_t *lens,
                  uint64_t n_reads);
+/* Append the reads of a reference PackedReads container AS THEY SIT IN MEMORY: `headers` points at its vector<PackedRead>
+ * (src/packed_reads.hpp:68-79, 136): n_reads records of header_stride bytes (0 = 16) = one 64-bit word of bit fields
+ * {is_allocated : 1, read_id : 47, read_len : 16} followed by the pointer to the read's bytes inside a 4 MB allocator block
+ * (src/linear_allocator_pool.cpp). Replaces the per-read unpack loop of count_kmers (src/kcount/kcount.cpp:71-77,
+ * src/packed_reads.cpp:196-208, 269-276): host threads gather the bytes piece by piece into pinned staging while the
+ * previous piece crosses PCIe; the offsets are built by a scan on the device. Returns when the last piece has been copied
+ * (the container may be released). */
+int kc_add_packed_reads(kc_ctx *ctx, const void *headers, uint64_t n_reads, uint32_t header_stride);
 int kc_clear_reads(kc_ctx *ctx);
 
 /* ---- the stage, phase by phase (all asynchronous on the context's stream unless noted) ----------- */

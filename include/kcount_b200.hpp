@@ -16,7 +16,9 @@
 // RPC store is replaced by the device-side bins + kc_exchange_* (multi-rank callers plug their transport into
 // KmerDHT::exchange_hook), and errors are C++ exceptions (kc_error) instead of DIE().
 #pragma once
+#include <chrono>
 #include <cstdint>
+#include <cstdio>
 #include <cstring>
 #include <functional>
 #include <memory>
@@ -173,6 +175,22 @@ class KmerDHT {
   double avg_kmer_count = 0;
   bool finished = false;
   int n_ranks = 1;
+  std::chrono::time_point<std::chrono::high_resolution_clock> start_t = std::chrono::high_resolution_clock::now();
+  // supermers handed in one at a time (add_supermer / HashTableInserter::insert_supermer): a supermer with count 1 IS a read
+  // as far as counting goes (interior k-mers, flanking bases as extensions, lower case = low quality:
+  // src/kcount/kcount_cpu.cpp:339-355), so they are buffered as PackedRead bytes and handed over in bulk
+  std::vector<uint8_t> sm_bytes;
+  std::vector<uint64_t> sm_offsets;
+  std::vector<uint16_t> sm_lens;
+  std::vector<std::pair<Kmer<MAX_K>, KmerCounts>> local_cache;  // local_kmers_begin / end
+  bool local_cached = false;
+
+  void flush_supermers() {
+    if (sm_lens.empty()) return;
+    ck(kc_add_reads(ctx, sm_bytes.data(), sm_bytes.size(), sm_offsets.data(), sm_lens.data(), sm_lens.size()));
+    ck(kc_sync(ctx));
+    sm_bytes.clear(), sm_offsets.clear(), sm_lens.clear();
+  }
 
   void ck(int rc) const {
     if (rc != KC_OK) throw kc_error(rc, kc_last_error(ctx));
@@ -208,6 +226,7 @@ class KmerDHT {
   KmerDHT &operator=(const KmerDHT &) = delete;
 
   kc_ctx *context() { return ctx; }
+  static size_t N() { return (size_t)Kmer<MAX_K>::N_LONGS; }
   void clear_stores() {}
   int get_minimizer_len() const { return (int)kc_minimizer_len(ctx); }
   uint64_t get_local_num_kmers() {
@@ -215,10 +234,28 @@ class KmerDHT {
     if (finished) ck(kc_result_size(ctx, 0, &n));
     return n;
   }
-  uint64_t get_num_kmers(bool /*all*/ = false) { return get_local_num_kmers(); }  // single rank; reduce over ranks in the caller
+  // sum over the ranks (kmer_dht.cpp:180-187): multi-rank callers plug their all-reduce in (upcxx::reduce_all there)
+  std::function<uint64_t(uint64_t)> reduce_sum_hook;
+  uint64_t get_num_kmers(bool /*all*/ = false) {
+    const uint64_t n = get_local_num_kmers();
+    return n_ranks > 1 && reduce_sum_hook ? reduce_sum_hook(n) : n;
+  }
+  void init_ctg_kmers() { throw kc_error(KC_ERR_ARG, "init_ctg_kmers: the contig k-mer pass is not on this path (src/kcount/kcount.cpp:150-153)"); }
+  int32_t get_time_offset_us() const {  // kmer_dht.cpp:310-313
+    return (int32_t)std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::high_resolution_clock::now() - start_t).count();
+  }
   int get_kmer_target_rank(const Kmer<MAX_K> &kmer, const Kmer<MAX_K> *kmer_rc = nullptr) const {  // kmer_dht.cpp:193-196
     Kmer<MAX_K> rc = kmer_rc ? *kmer_rc : kmer.revcomp();
     return kc_owner_of(ctx, (rc < kmer ? rc : kmer).longs);
+  }
+  // a batch of get_local_kmer_counts in one kernel launch (count 0 = absent): what a traversal should call
+  void get_local_kmer_counts_batch(const Kmer<MAX_K> *kmers, uint64_t n, KmerCounts *out) {
+    std::vector<uint64_t> q(n * N());
+    std::vector<uint16_t> c(n);
+    std::vector<char> l(n), r(n);
+    for (uint64_t i = 0; i < n; i++) std::memcpy(&q[i * N()], kmers[i].longs, N() * sizeof(uint64_t));
+    if (n) ck(kc_lookup(ctx, q.data(), n, c.data(), l.data(), r.data()));
+    for (uint64_t i = 0; i < n; i++) out[i] = KmerCounts{nullptr, c[i], l[i], r[i]};
   }
   KmerCounts *get_local_kmer_counts(const Kmer<MAX_K> &kmer) {  // kmer_dht.cpp:199-207; pointer valid until the next call
     static thread_local KmerCounts kc;
@@ -251,7 +288,30 @@ class KmerDHT {
       ck(kc_add_reads(ctx, pr.raw_bytes().data(), pr.raw_bytes().size(), pr.raw_offsets().data(), pr.raw_lens().data(),
                       pr.get_local_num_reads()));
   }
+  // kmer_dht.cpp:248-251. The reference ships the supermer to target_rank by RPC; here the device cuts and routes by owner
+  // itself, so the target is only checked
+  void add_supermer(Supermer &supermer, int target_rank) {
+    if (target_rank < 0 || target_rank >= n_ranks) throw kc_error(KC_ERR_ARG, "add_supermer: bad target rank");
+    add_supermer_seq(supermer.seq, supermer.count);
+  }
+  void add_supermer_seq(const std::string &seq, kmer_count_t count) {
+    if (count != 1) throw kc_error(KC_ERR_ARG, "add_supermer: count != 1 (contig k-mers) is not on this path");
+    sm_offsets.push_back(sm_bytes.size());
+    sm_lens.push_back((uint16_t)seq.size());
+    for (char ch : seq) {
+      uint8_t b = 4;
+      switch (ch & ~0x20) {
+        case 'A': b = 0; break;
+        case 'C': b = 1; break;
+        case 'G': b = 2; break;
+        case 'T': b = 3; break;
+      }
+      sm_bytes.push_back((uint8_t)(b | ((ch >= 'A' && ch <= 'Z') ? 31 << 3 : 0)));  // upper case = high quality
+    }
+    if (sm_bytes.size() >= (64u << 20)) flush_supermers();
+  }
   void flush_updates() {  // kmer_dht.cpp:253-258
+    flush_supermers();
     ck(kc_parse(ctx));
     if (n_ranks > 1) {
       if (!exchange_hook) throw kc_error(KC_ERR_STATE, "multi-rank KmerDHT needs an exchange_hook");
@@ -263,6 +323,16 @@ class KmerDHT {
     ck(kc_finalize(ctx, &stats));
     avg_kmer_count = stats.avg_kmer_count;
     finished = true;
+    local_cached = false;
+  }
+  // what count_kmers / insert_into_local_hashtable log at this point (src/kcount/kcount.cpp:94-102, kcount_cpu.cpp:497-520)
+  void log_stage_counters(FILE *f = stderr) const {
+    fprintf(f, "Processed a total of %llu reads %llu raw kmers\n", (unsigned long long)stats.n_reads, (unsigned long long)stats.raw_kmers);
+    fprintf(f, "Supermer inserts %llu (rank-local; avg / max / load come from the caller's reduction)\n", (unsigned long long)stats.supermers_in);
+    fprintf(f, "Number of elements in hash table: %llu, purged %llu, dropped %llu\n", (unsigned long long)stats.unique_kmers,
+            (unsigned long long)stats.purged_kmers, (unsigned long long)stats.dropped);
+    fprintf(f, "Total kmers %llu, kmer count sum %llu, avg %.3f, max %llu\n", (unsigned long long)stats.final_kmers,
+            (unsigned long long)stats.sum_counts, stats.avg_kmer_count, (unsigned long long)stats.max_count);
   }
   void dump_kmers(const std::string &path = "") {  // kmer_dht.cpp:274-297 (here: sorted, uncompressed)
     std::string p = path.empty() ? "kmers-" + std::to_string(Kmer<MAX_K>::get_k()) + ".txt" : path;
@@ -283,6 +353,23 @@ class KmerDHT {
   void set_result_sink(uint64_t *keys, uint16_t *counts, char *left, char *right, uint64_t capacity) {
     ck(kc_set_result_sink(ctx, keys, counts, left, right, capacity));
   }
+  // local_kmers_begin / local_kmers_end (kmer_dht.cpp:300-307): `it->first` is the Kmer, `it->second` the KmerCounts, as with
+  // the reference's map iterator; the entries are materialised on the host by the first call after finish_updates
+  using local_iterator = typename std::vector<std::pair<Kmer<MAX_K>, KmerCounts>>::iterator;
+  local_iterator local_kmers_begin() {
+    if (!local_cached) {
+      LocalKmers lk = local_kmers(false);
+      local_cache.clear();
+      local_cache.reserve(lk.size());
+      for (size_t i = 0; i < lk.size(); i++) local_cache.emplace_back(lk.kmer(i), lk.counts_of(i));
+      local_cached = true;
+    }
+    return local_cache.begin();
+  }
+  local_iterator local_kmers_end() {
+    local_kmers_begin();
+    return local_cache.end();
+  }
   LocalKmers local_kmers(bool sorted = false) {
     LocalKmers r;
     uint64_t n = get_local_num_kmers();
@@ -293,6 +380,49 @@ class KmerDHT {
     r.right.resize(n);
     if (n) ck(kc_result_copy(ctx, 0, r.keys.data(), r.counts.data(), r.left.data(), r.right.data(), nullptr));
     return r;
+  }
+};
+
+// ---- the reference's own plug point (chosen at link time there, src/kcount/CMakeLists.txt:24-69), for callers that drive the
+// stage read by read / supermer by supermer. integration/kcount_b200_glue.cpp is the same thing against the reference's
+// real class declarations.
+template <int MAX_K>
+struct SeqBlockInserter {  // src/kcount/kcount.hpp:56-68
+  int qual_offset, minimizer_len;
+  SeqBlockInserter(int qual_offset, int minimizer_len) : qual_offset(qual_offset), minimizer_len(minimizer_len) {}
+  // seq: the read with low-quality bases already in lower case (count_kmers, src/kcount/kcount.cpp:80-85)
+  void process_seq(std::string &seq, kmer_count_t depth, dist_object<KmerDHT<MAX_K>> &kmer_dht) {
+    if (depth > 1) throw kc_error(KC_ERR_ARG, "process_seq: depth > 1 (contig k-mers) is not on this path");
+    kmer_dht->add_supermer_seq(seq, 1);
+  }
+  void done_processing(dist_object<KmerDHT<MAX_K>> &) {}
+};
+
+template <int MAX_K>
+class HashTableInserter {  // src/kcount/kmer_dht.hpp:95-116, over an existing KmerDHT's stage
+  KmerDHT<MAX_K> *dht = nullptr;
+  std::chrono::duration<double> t_insert{0};
+
+ public:
+  void attach(KmerDHT<MAX_K> &d) { dht = &d; }
+  void init(size_t, size_t, size_t, bool) {}  // sizing happened in the KmerDHT constructor (est_kmers)
+  void init_ctg_kmers(size_t) { throw kc_error(KC_ERR_ARG, "init_ctg_kmers: not on this path"); }
+  void insert_supermer(const std::string &supermer_seq, kmer_count_t supermer_count) { dht->add_supermer_seq(supermer_seq, supermer_count); }
+  void flush_inserts() {
+    auto t0 = std::chrono::high_resolution_clock::now();
+    dht->flush_updates();
+    t_insert += std::chrono::high_resolution_clock::now() - t0;
+  }
+  double insert_into_local_hashtable() {
+    auto t0 = std::chrono::high_resolution_clock::now();
+    dht->finish_updates();
+    t_insert += std::chrono::high_resolution_clock::now() - t0;
+    return dht->get_avg_kmer_count();
+  }
+  void get_elapsed_time(double &insert_time, double &kernel_time) {
+    insert_time = t_insert.count();
+    const kc_stats &s = dht->get_stats();
+    kernel_time = (s.ms_parse + s.ms_insert + s.ms_finalize) / 1e3;
   }
 };
 

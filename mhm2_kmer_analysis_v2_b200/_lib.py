@@ -65,6 +65,7 @@ PROTOTYPES = {
     "kc_version": (C.c_char_p, []),
     "kc_device_count": (C.c_int, []),
     "kc_add_reads": (C.c_int, [vp, vp, C.c_uint64, vp, vp, C.c_uint64]),
+    "kc_add_packed_reads": (C.c_int, [vp, vp, C.c_uint64, C.c_uint32]),
     "kc_clear_reads": (C.c_int, [vp]),
     "kc_parse": (C.c_int, [vp]),
     "kc_exchange_send_sizes": (C.c_int, [vp, vp]),
@@ -108,6 +109,7 @@ SYNTH_PROTOTYPES = {
     "kc_synth_destroy": (None, [vp]),
     "kc_synth_generate": (C.c_int, [vp, C.c_uint64, C.c_uint64, vp, vp, vp, C.POINTER(C.c_uint64), C.c_int]),
     "kc_reads_save": (C.c_int, [C.c_char_p, vp, C.c_uint64, vp, vp, C.c_uint64]),
+    "kc_reads_to_packed_layout": (C.c_int, [vp, vp, vp, C.c_uint64, vp, C.c_uint64, C.c_uint64, vp, C.POINTER(C.c_uint64)]),
 }
 SYNTH_LIB_PATH = os.path.join(HERE, "libkc_synth.so")
 

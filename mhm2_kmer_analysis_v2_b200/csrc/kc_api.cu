@@ -2,12 +2,15 @@
 // Host C++ only calls CUDA from here; no CUDA type crosses the ABI. There is no CPU fallback anywhere: every phase is a
 // kernel launch on the context's stream.
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
 #include <numeric>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "kc_internal.h"
@@ -75,6 +78,12 @@ struct kc_ctx {
   std::vector<cudaEvent_t> ev_in_pool;
   size_t ev_in_used = 0;
   ReadChunk spare;  // buffers of the last kc_clear_reads, reused by the next kc_add_reads
+  // kc_add_packed_reads: the reads of a PackedReads container are gathered into two pinned staging buffers by host threads
+  // and copied from there; ev_stage[i] = the copy out of buffer i has completed
+  uint8_t *h_stage[2] = {nullptr, nullptr};
+  cudaEvent_t ev_stage[2] = {nullptr, nullptr};
+  bool stage_busy[2] = {false, false};
+  double packed_gather_ms = 0;
   cudaEvent_t ev_slice[kSinkSlices];
   unsigned long long *h_slice_n = nullptr;  // pinned: n_final after every slice
   unsigned long long *h_pinned = nullptr;   // pinned staging [kPinnedWords]
@@ -501,6 +510,10 @@ extern "C" void kc_destroy(kc_ctx *c) {
       if (arr[i]) cudaEventDestroy(arr[i]);
   for (auto &xs : c->xfer_stream)
     if (xs) cudaStreamDestroy(xs);
+  for (int i = 0; i < 2; i++) {
+    if (c->h_stage[i]) cudaFreeHost(c->h_stage[i]);
+    if (c->ev_stage[i]) cudaEventDestroy(c->ev_stage[i]);
+  }
   if (c->h_slice_n) cudaFreeHost(c->h_slice_n);
   if (c->h_pinned) cudaFreeHost(c->h_pinned);
   dev_free(c->d_scratch);
@@ -617,6 +630,138 @@ extern "C" int kc_add_reads(kc_ctx *c, const uint8_t *bytes, uint64_t n_bytes, c
   c->n_bases += n_bytes;
   c->caps_valid = false;
   c->phase = PH_EMPTY;
+  return KC_OK;
+}
+
+// ---- the reference's real in-memory reads ---------------------------------------------------
+// PackedReads keeps a vector<PackedRead> of 16-byte headers (src/packed_reads.hpp:68-79: one 64-bit word of bit fields --
+// is_allocated : 1, read_id : 47, read_len : 16, from the low bit up -- and a pointer to the read's bytes), the bytes
+// themselves bump-allocated in 4 MB blocks (src/packed_reads.hpp:136, src/linear_allocator_pool.cpp). count_kmers walks them
+// with get_next_read and unpacks every read into two strings (src/packed_reads.cpp:196-208, 269-276). Here host threads
+// gather the bytes of whole pieces of the container into pinned staging (two buffers: one is filled while the other is
+// copied), the lengths go up as they are and the offsets are made by a scan on the device.
+static const uint64_t kStageBytes = 64ull << 20;
+static const uint64_t kGatherBlock = 4096;  // reads per unit of host work
+
+struct PackedHeader {
+  uint64_t bits;
+  const uint8_t *bytes;
+};
+
+template <typename F>
+static void parallel_blocks(uint64_t n_blocks, int n_threads, F fn) {
+  if (n_threads <= 1 || n_blocks <= 1) {
+    for (uint64_t b = 0; b < n_blocks; b++) fn(b);
+    return;
+  }
+  std::atomic<uint64_t> next{0};
+  std::vector<std::thread> th;
+  for (int t = 0; t < n_threads; t++)
+    th.emplace_back([&]() {
+      for (uint64_t b = next.fetch_add(1); b < n_blocks; b = next.fetch_add(1)) fn(b);
+    });
+  for (auto &x : th) x.join();
+}
+
+extern "C" int kc_add_packed_reads(kc_ctx *c, const void *headers, uint64_t n_reads, uint32_t header_stride) {
+  if (!c || (n_reads && !headers)) return fail(c, KC_ERR_ARG, "kc_add_packed_reads: null argument");
+  if (header_stride == 0) header_stride = sizeof(PackedHeader);
+  if (header_stride < sizeof(PackedHeader)) return fail(c, KC_ERR_ARG, "kc_add_packed_reads: header stride %u < 16", header_stride);
+  if (n_reads == 0) return KC_OK;
+  CK(cudaSetDevice(c->device));
+  const auto t_begin = std::chrono::high_resolution_clock::now();
+  auto hdr = [&](uint64_t i) { return reinterpret_cast<const PackedHeader *>(static_cast<const uint8_t *>(headers) + i * header_stride); };
+  int n_threads = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+  if (const char *e = getenv("KC_HOST_THREADS")) n_threads = std::max(1, atoi(e));
+  // pass 0: lengths and bytes per block of reads
+  const uint64_t n_blocks = (n_reads + kGatherBlock - 1) / kGatherBlock;
+  std::vector<uint16_t> lens(n_reads);
+  std::vector<uint64_t> block_base(n_blocks + 1, 0);
+  parallel_blocks(n_blocks, n_threads, [&](uint64_t b) {
+    const uint64_t r1 = std::min(n_reads, (b + 1) * kGatherBlock);
+    uint64_t sum = 0;
+    for (uint64_t r = b * kGatherBlock; r < r1; r++) {
+      const uint16_t len = (uint16_t)(hdr(r)->bits >> 48);
+      lens[r] = len;
+      sum += len;
+    }
+    block_base[b + 1] = sum;
+  });
+  for (uint64_t b = 0; b < n_blocks; b++) block_base[b + 1] += block_base[b];
+  const uint64_t n_bytes = block_base[n_blocks];
+  ReadChunk ch;
+  if (c->spare.d_bytes && c->spare.cap_bytes >= n_bytes + 16 && c->spare.cap_reads >= n_reads) {
+    ch = c->spare;
+    c->spare = ReadChunk();
+  } else {
+    ch.cap_bytes = n_bytes + 16;
+    ch.cap_reads = n_reads;
+    CK(dev_alloc(&ch.d_bytes, ch.cap_bytes));
+    CK(dev_alloc(&ch.d_offsets, n_reads));
+    CK(dev_alloc(&ch.d_lens, n_reads));
+  }
+  ch.owner = true;
+  for (int i = 0; i < 2; i++) {
+    if (!c->h_stage[i]) CK(cudaHostAlloc((void **)&c->h_stage[i], kStageBytes, cudaHostAllocDefault));
+    if (!c->ev_stage[i]) CK(cudaEventCreateWithFlags(&c->ev_stage[i], cudaEventDisableTiming));
+  }
+  CK(cudaMemcpyAsync(ch.d_lens, lens.data(), n_reads * sizeof(uint16_t), cudaMemcpyHostToDevice, c->in_stream));
+  CK(scan_lens_to_offsets(ch.d_lens, ch.d_offsets, n_reads, c->in_stream, &c->launches));
+  auto next_event = [&](cudaEvent_t *ev) -> cudaError_t {
+    if (c->ev_in_used == c->ev_in_pool.size()) {
+      cudaEvent_t e;
+      cudaError_t rc = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+      if (rc != cudaSuccess) return rc;
+      c->ev_in_pool.push_back(e);
+    }
+    *ev = c->ev_in_pool[c->ev_in_used++];
+    return cudaSuccess;
+  };
+  // pieces of whole blocks, at most one staging buffer each
+  int which = 0;
+  bool first = true;
+  for (uint64_t b0 = 0; b0 < n_blocks;) {
+    uint64_t b1 = b0 + 1;
+    while (b1 < n_blocks && block_base[b1 + 1] - block_base[b0] <= kStageBytes) b1++;
+    const uint64_t piece_bytes = block_base[b1] - block_base[b0];
+    if (piece_bytes > kStageBytes) return fail(c, KC_ERR_ARG, "kc_add_packed_reads: %llu reads of more than %llu bytes", (unsigned long long)kGatherBlock, (unsigned long long)kStageBytes);
+    if (c->stage_busy[which]) CK(cudaEventSynchronize(c->ev_stage[which]));
+    uint8_t *stage = c->h_stage[which];
+    parallel_blocks(b1 - b0, n_threads, [&](uint64_t bi) {
+      const uint64_t b = b0 + bi, r1 = std::min(n_reads, (b + 1) * kGatherBlock);
+      uint8_t *dst = stage + (block_base[b] - block_base[b0]);
+      for (uint64_t r = b * kGatherBlock; r < r1; r++) {
+        const PackedHeader *h = hdr(r);
+        const uint16_t len = lens[r];
+        if (len) memcpy(dst, h->bytes, len);
+        dst += len;
+      }
+    });
+    if (piece_bytes) CK(cudaMemcpyAsync(ch.d_bytes + block_base[b0], stage, piece_bytes, cudaMemcpyHostToDevice, c->in_stream));
+    CK(cudaEventRecord(c->ev_stage[which], c->in_stream));
+    c->stage_busy[which] = true;
+    ReadChunk sub = ch;
+    sub.owner = first;
+    const uint64_t r0 = b0 * kGatherBlock, r1 = std::min(n_reads, b1 * kGatherBlock);
+    sub.d_offsets = ch.d_offsets + r0;
+    sub.d_lens = ch.d_lens + r0;
+    sub.n_reads = r1 - r0;
+    sub.n_bytes = piece_bytes;
+    CK(next_event(&sub.ready));
+    CK(cudaEventRecord(sub.ready, c->in_stream));
+    c->chunks.push_back(sub);
+    first = false;
+    which ^= 1;
+    b0 = b1;
+  }
+  // `lens` is a local: its copy has to be out before it goes away (the staging buffers are the context's)
+  CK(cudaStreamSynchronize(c->in_stream));
+  c->stage_busy[0] = c->stage_busy[1] = false;
+  c->n_reads += n_reads;
+  c->n_bases += n_bytes;
+  c->caps_valid = false;
+  c->phase = PH_EMPTY;
+  c->packed_gather_ms = std::chrono::duration<double, std::milli>(std::chrono::high_resolution_clock::now() - t_begin).count();
   return KC_OK;
 }
 
@@ -1358,12 +1503,15 @@ static int insert_resident(kc_ctx *c, const std::vector<uint8_t *> &src_in) {
   uint64_t cap = c->last_final ? c->last_final + c->last_final / 8 + 1024 : occ / 6 + 1024;
   if (keep_ext) cap = std::max<uint64_t>(cap, c->last_ext ? c->last_ext + c->last_ext / 8 + 1024 : occ / 3 + 1024);
   cap = std::min<uint64_t>(cap, occ / 2 + 1024);
-  size_t free_b = 0, total_b = 0;
-  CK(cudaMemGetInfo(&free_b, &total_b));
-  const uint64_t per_entry = (uint64_t)c->N * 8 + 4 + (keep_ext ? (uint64_t)c->N * 8 + 20 : 0);
-  const uint64_t have = (c->res_final.cap * ((uint64_t)c->N * 8 + 4)) + (c->res_ext.cap * ((uint64_t)c->N * 8 + 20));
-  const uint64_t budget = c->cfg.mem_budget_bytes ? c->cfg.mem_budget_bytes : (uint64_t)((free_b + have) * 0.7);
-  if (cap * per_entry > budget) cap = std::max<uint64_t>(budget / per_entry, 1024);
+  const bool have_room = c->res_final.keys && c->res_final.cap >= cap && (!keep_ext || (c->res_ext.ext8 && c->res_ext.cap >= cap));
+  if (!have_room) {  // (a driver query per pass is not free: only when something has to be allocated)
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    const uint64_t per_entry = (uint64_t)c->N * 8 + 4 + (keep_ext ? (uint64_t)c->N * 8 + 20 : 0);
+    const uint64_t have = (c->res_final.cap * ((uint64_t)c->N * 8 + 4)) + (c->res_ext.cap * ((uint64_t)c->N * 8 + 20));
+    const uint64_t budget = c->cfg.mem_budget_bytes ? c->cfg.mem_budget_bytes : (uint64_t)((free_b + have) * 0.7);
+    if (cap * per_entry > budget) cap = std::max<uint64_t>(budget / per_entry, 1024);
+  }
   if (c->res_final.cap < cap || !c->res_final.keys) {
     int rc = alloc_results(c, c->res_final, cap, false);
     if (rc) return rc;

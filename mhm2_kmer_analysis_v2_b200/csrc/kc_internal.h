@@ -233,6 +233,9 @@ cudaError_t launch_index_lookup(const IndexParams &p, const uint64_t *queries, u
 cudaError_t sort_result_by_key(uint64_t *keys, uint16_t *counts, char *left, char *right, uint16_t *ext8, uint64_t n, int n_words, int sm_count,
                                cudaStream_t s, uint64_t *launches);
 
+// offsets[i] = sum of lens[0 .. i) (device arrays)
+cudaError_t scan_lens_to_offsets(const uint16_t *lens, uint64_t *offsets, uint64_t n, cudaStream_t s, uint64_t *launches);
+
 static const int kHeaderAlign = 64;
 
 // ---- slices of the bin range: the receive copies, the refine pass, the count pass and the result hand-off all work slice

@@ -7,6 +7,7 @@
 // arrays are then gathered once through the final permutation. cub is the CUDA toolkit's own library (this is a plain
 // library sort, not one of the stage's kernels).
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #include "kc_internal.h"
 
@@ -86,6 +87,29 @@ cudaError_t sort_result_by_key(uint64_t *keys, uint16_t *counts, char *left, cha
   if (e == cudaSuccess) e = gather_in_place<char, 1>(right, perm[0], n, tmp, grid, s, launches);
   if (e == cudaSuccess && ext8) e = gather_in_place<uint16_t, 8>(ext8, perm[0], n, tmp, grid, s, launches);
   return done(e);
+}
+
+// offsets of the reads inside the packed byte stream from their lengths (kc_add_packed_reads): lengths widened to 64 bits
+// in place of the offsets, then the toolkit's exclusive scan over them (input-side helper, not a stage kernel).
+__global__ void widen_lens_kernel(const uint16_t *__restrict__ lens, uint64_t *__restrict__ out, uint64_t n) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = lens[i];
+}
+
+cudaError_t scan_lens_to_offsets(const uint16_t *lens, uint64_t *offsets, uint64_t n, cudaStream_t s, uint64_t *launches) {
+  if (n == 0) return cudaSuccess;
+  if (n > 0x7fffffffULL) return cudaErrorInvalidValue;
+  widen_lens_kernel<<<(int)std::min<uint64_t>((n + 255) / 256, 148 * 8), 256, 0, s>>>(lens, offsets, n);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  size_t temp_bytes = 0;
+  if ((e = cub::DeviceScan::ExclusiveSum(nullptr, temp_bytes, offsets, offsets, (int)n, s)) != cudaSuccess) return e;
+  void *temp = nullptr;
+  if ((e = cudaMallocAsync(&temp, temp_bytes ? temp_bytes : 1, s)) != cudaSuccess) return e;
+  e = cub::DeviceScan::ExclusiveSum(temp, temp_bytes, offsets, offsets, (int)n, s);
+  (*launches) += 3;
+  cudaFreeAsync(temp, s);
+  return e;
 }
 
 }  // namespace kc

@@ -261,3 +261,32 @@ int kc_reads_save(const char *path, const uint8_t *bytes, uint64_t n_bytes, cons
   fclose(f);
   return ok ? KC_SYNTH_OK : KC_SYNTH_ERR_IO;
 }
+
+/* Lays a read set out the way the reference's PackedReads holds it in memory (src/packed_reads.hpp:68-79, 136): 16-byte
+ * PackedRead headers {is_allocated : 1, read_id : 47, read_len : 16 | unsigned char *bytes}, the bytes bump-allocated in
+ * blocks of block_bytes (4 MB there; a read never straddles two blocks, src/linear_allocator_pool.cpp). The blocks are
+ * placed in `arena` in DESCENDING address order, so consecutive blocks are never adjacent in memory. */
+int kc_reads_to_packed_layout(const uint8_t *bytes, const uint64_t *offsets, const uint16_t *lens, uint64_t n_reads, uint8_t *arena,
+                              uint64_t arena_bytes, uint64_t block_bytes, uint64_t *headers /* [2 * n_reads] */, uint64_t *blocks_used) {
+  if (!bytes || !offsets || !lens || !arena || !headers || block_bytes == 0) return -1;
+  const uint64_t n_blocks_total = arena_bytes / block_bytes;
+  uint64_t blk = 0, used = block_bytes; /* force a first block */
+  uint8_t *base = NULL;
+  for (uint64_t i = 0; i < n_reads; i++) {
+    const uint64_t len = lens[i];
+    if (len > block_bytes) return -1;
+    if (used + len > block_bytes) {
+      if (blk == n_blocks_total) return -3;
+      base = arena + (n_blocks_total - 1 - blk) * block_bytes;
+      blk++;
+      used = 0;
+    }
+    memcpy(base + used, bytes + offsets[i], len);
+    const int64_t id = (i & 1) ? (int64_t)(i / 2 + 1) : -(int64_t)(i / 2 + 1); /* pair 1 negative, pair 2 positive */
+    headers[2 * i] = 1ull | (((uint64_t)id & ((1ull << 47) - 1)) << 1) | (len << 48);
+    headers[2 * i + 1] = (uint64_t)(uintptr_t)(base + used);
+    used += len;
+  }
+  if (blocks_used) *blocks_used = blk;
+  return 0;
+}

@@ -75,6 +75,11 @@ class KcountStage:
                                      reads.lens.ctypes.data, len(reads.lens)))
         self._keepalive.append(reads)  # async copies from pinned memory may still be in flight
 
+    def add_packed_reads(self, container):
+        """container: reads.PackedReadsLayout -- the reference's in-memory PackedReads (16-byte headers pointing into 4 MB
+        allocator blocks). Returns when the bytes are on the device."""
+        self._ck(self.L.kc_add_packed_reads(self.h, container.headers.ctypes.data, len(container), 16))
+
     def add_reads_ptr(self, bytes_ptr, n_bytes, offsets_ptr, lens_ptr, n_reads):
         """Raw pointers (host pinned or device), e.g. torch tensors' data_ptr()."""
         self._ck(self.L.kc_add_reads(self.h, bytes_ptr, n_bytes, offsets_ptr, lens_ptr, n_reads))

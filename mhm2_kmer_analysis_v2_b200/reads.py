@@ -69,6 +69,31 @@ class ReadSet:
         return ReadSet(bs, np.concatenate(offs), lens)
 
 
+class PackedReadsLayout:
+    """A ReadSet laid out as the reference's PackedReads holds it in memory (src/packed_reads.hpp:68-79, 136): a contiguous
+    array of 16-byte PackedRead headers (bit fields + pointer) and the read bytes bump-allocated in 4 MB blocks. The blocks
+    live in `arena` (kept alive here) in descending address order. Input of KcountStage.add_packed_reads."""
+
+    BLOCK = 4 * 1024 * 1024
+
+    def __init__(self, reads, block_bytes=BLOCK):
+        n = len(reads)
+        # a read never straddles two blocks: the tail of a block may stay empty
+        per_block = max(block_bytes - int(reads.lens.max(initial=0)), 1)
+        n_blocks = len(reads.bytes) // per_block + 2
+        self.arena = np.empty(n_blocks * block_bytes, np.uint8)
+        self.headers = np.empty((n, 2), np.uint64)
+        used = C.c_uint64()
+        rc = _lib.synth_lib().kc_reads_to_packed_layout(reads.bytes.ctypes.data, reads.offsets.ctypes.data, reads.lens.ctypes.data, n,
+                                                        self.arena.ctypes.data, len(self.arena), block_bytes, self.headers.ctypes.data, C.byref(used))
+        if rc:
+            raise _lib.KcError(rc, "kc_reads_to_packed_layout")
+        self.n_blocks = used.value
+
+    def __len__(self):
+        return len(self.headers)
+
+
 class PinnedBuffer:
     """Page-locked host memory from kc_host_alloc (cudaHostAlloc), viewed as a numpy u8 array."""
 

@@ -4,6 +4,7 @@
 // exit 0 = ok, 42 = no CUDA device (KC_ERR_CUDA, the library has no CPU path), anything else = failure.
 #include <cstdio>
 #include <cstdlib>
+#include <string>
 #include <vector>
 
 #include "kc_synth.h"
@@ -48,6 +49,41 @@ static int run(unsigned k, uint64_t n_reads, uint64_t seed, const char *dump) {
     if (!kmer_dht->kmer_exists(km.revcomp())) return 5;
     if (kmer_dht->get_kmer_count(km) != lk.counts[i]) return 6;
     if (kmer_dht->get_kmer_target_rank(km) != 0) return 7;
+  }
+  // the plug-point route: the same reads, one at a time through SeqBlockInserter::process_seq (lower case = low quality,
+  // as count_kmers prepares them) into a second KmerDHT; its table must be the first one's
+  {
+    dist_object<KmerDHT<MAX_K>> dht2(my_num_kmers, (size_t)0, (size_t)0, 100, false, 4);
+    SeqBlockInserter<MAX_K> sbi(qual_offset, dht2->get_minimizer_len());
+    std::string seq;
+    for (uint64_t i = 0; i < n_reads; i++) {
+      if (len[i] < k) continue;
+      seq.resize(len[i]);
+      for (unsigned j = 0; j < len[i]; j++) {
+        const uint8_t b = bytes[off[i] + j];
+        const char c = "ACGTN"[(b & 7) > 4 ? 4 : (b & 7)];
+        seq[j] = (b >> 3) < 20 ? (char)(c | 0x20) : c;
+      }
+      sbi.process_seq(seq, 0, dht2);
+    }
+    sbi.done_processing(dht2);
+    HashTableInserter<MAX_K> hti;
+    hti.attach(*dht2);
+    hti.flush_inserts();
+    const double avg = hti.insert_into_local_hashtable();
+    if (dht2->get_num_kmers() != kmer_dht->get_num_kmers() || avg != kmer_dht->get_avg_kmer_count()) return 8;
+    // local_kmers_begin / end, and a batch of lookups against the first table
+    std::vector<Kmer<MAX_K>> ks;
+    std::vector<KmerCounts> want;
+    for (auto it = dht2->local_kmers_begin(); it != dht2->local_kmers_end() && ks.size() < 5000; ++it) {
+      ks.push_back(it->first);
+      want.push_back(it->second);
+    }
+    std::vector<KmerCounts> got(ks.size());
+    kmer_dht->get_local_kmer_counts_batch(ks.data(), ks.size(), got.data());
+    for (size_t i = 0; i < ks.size(); i++)
+      if (got[i].count != want[i].count || got[i].left != want[i].left || got[i].right != want[i].right) return 9;
+    if (dht2->get_time_offset_us() <= 0) return 11;
   }
   printf("{\"k\": %u, \"kmers\": %llu, \"avg_kmer_count\": %.9f, \"supermer_inserts\": %llu, \"m\": %d}\n", k,
          (unsigned long long)kmer_dht->get_num_kmers(), kmer_dht->get_avg_kmer_count(),

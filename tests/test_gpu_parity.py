@@ -144,3 +144,24 @@ def test_long_reads_span_several_segments(oracle_mod, k, read_len):
     assert stats["inserted_kmers"] == reads.counted_kmers(k)
     assert_same(st.result(True), o.result(True), f"k={k} read_len={read_len}")
     st.close()
+
+
+@pytest.mark.parametrize("k,block", [(21, 1 << 16), (33, 4 << 20), (55, 1 << 14)])
+def test_packed_reads_container_as_input(oracle_mod, k, block):
+    """kc_add_packed_reads: the reference's in-memory PackedReads (16-byte PackedRead headers pointing into bump-allocated
+    blocks, src/packed_reads.hpp:68-79, 136) goes in as it is; same table as the oracle's, same as the flat input."""
+    reads = K.generate(None, 30_000, seed=900 + k, n_genomes=3, genome_len_min=30_000, genome_len_max=60_000, abundance_sigma=1.0,
+                       sub_rate=0.005, read_len_min=60, n_rate=0.001)
+    layout = K.PackedReadsLayout(reads, block_bytes=block)
+    assert layout.n_blocks > 1 or block >= (4 << 20)
+    o = oracle_run(oracle_mod, reads, k)
+    st = K.KcountStage(k, keep_ext_counts=True)
+    st.add_packed_reads(layout)
+    st.add_packed_reads(layout)  # twice, then cleared: containers append like kc_add_reads
+    st.clear_reads()
+    st.add_packed_reads(layout)
+    stats = st.run()
+    assert stats["n_reads"] == len(reads) and stats["counted_kmers"] == reads.counted_kmers(k)
+    assert_same(st.result(True), o.result(True), f"packed reads k={k}")
+    assert st.checksum(False) == o.checksum(False)
+    st.close()
