@@ -242,13 +242,8 @@ struct WarpCtx {
 
 // Stage records [c0, c0 + n) of the bin (an index space over the concatenated source segments) and build the
 // occurrence map. Returns the number of k-mer occurrences in the chunk; n_nonempty = records that carry any.
-// `more`: the bin goes on behind these n records. The walk takes 32 occurrences per step, so a chunk leaves on average half
-// a step of idle lanes behind; when another chunk follows anyway, the cut is moved back by up to 15 records to where the
-// occurrence count comes closest below a multiple of 32 (n_taken <= n; the records behind the cut are staged again with the
-// next chunk, out of L2). Measured on C2: 12.7 % of the walk steps' lanes were idle, 7.5 points of that at chunk seams.
 template <int R>
-__device__ __forceinline__ uint32_t stage_chunk(const CountParams &p, WarpCtx &wc, uint32_t c0, int n, bool more, uint32_t &n_nonempty,
-                                                uint32_t &n_taken) {
+__device__ __forceinline__ uint32_t stage_chunk(const CountParams &p, WarpCtx &wc, uint32_t c0, int n, uint32_t &n_nonempty) {
   constexpr int W = R / 4;
   constexpr int U = R / 16;
   const uint32_t lane = lane_id();
@@ -309,24 +304,7 @@ __device__ __forceinline__ uint32_t stage_chunk(const CountParams &p, WarpCtx &w
     rank0 += (uint32_t)__popc(m_nz);
   }
   n_nonempty = rank0;
-  n_taken = (uint32_t)n;
   __syncwarp();
-  if (more && rank0 > 16u && (run & 31u) != 0u) {
-    // lane i < 16: cut behind the non-empty record of rank rank0 - 1 - i
-    const uint32_t i = lane & 15u;
-    const uint32_t occ_t = i == 0u ? run : (uint32_t)wc.s_pre[rank0 - i];
-    const uint32_t waste = (32u - (occ_t & 31u)) & 31u;
-    uint32_t best = (waste << 5) | i;
-#pragma unroll
-    for (int o = 8; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
-    const uint32_t bi = best & 31u;
-    if (bi != 0u) {
-      const uint32_t t = rank0 - 1u - bi;
-      n_taken = (uint32_t)wc.s_nz[t] + 1u;
-      n_nonempty = t + 1u;
-      run = (uint32_t)wc.s_pre[t + 1u];
-    }
-  }
   return run;
 }
 
@@ -438,11 +416,9 @@ __device__ __forceinline__ bool walk_bin(const CountParams &p, const Table<N> &t
                                          uint32_t &n_records, unsigned long long &n_occ) {
   const uint32_t total = wc.n_rec;
   bool overflow = false;
-  uint32_t taken = 0;
-  for (uint32_t c0 = 0; c0 < total && !overflow; c0 += taken) {
+  for (uint32_t c0 = 0; c0 < total && !overflow; c0 += (uint32_t)cap_rec) {
     uint32_t n_nz = 0;
-    const uint32_t n = min((uint32_t)cap_rec, total - c0);
-    const uint32_t occ = stage_chunk<R>(p, wc, c0, (int)n, total - c0 > n, n_nz, taken);
+    const uint32_t occ = stage_chunk<R>(p, wc, c0, (int)min((uint32_t)cap_rec, total - c0), n_nz);
     n_records += n_nz;
     n_occ += occ;
     if (occ) walk_chunk<N, R, HEAVY, (HEAVY ? 1 : CW_ILP)>(p, tb, wc, occ, n_nz, claimed, overflow);

@@ -220,10 +220,205 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(RefineParams p) {
   }
 }
 
+// ---- bulk asynchronous copies (sm_90+ / sm_100a: cp.async.bulk + mbarrier; SASS UBLKCP / SYNCS) ----------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+// global (local HBM or a peer's, mapped) -> this CTA's shared memory; completion is counted in bytes on `bar`
+__device__ __forceinline__ void bulk_load(void *dst_smem, const void *src, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)), "l"(src),
+               "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// ---- step B, bulk-copy variant: the coarse bins of a CTA are DOUBLE BUFFERED. While the CTA histograms and scatters bin i
+// out of one stage buffer, the segments of bin i + 1 (one contiguous run per source rank, local or in a peer's memory) are
+// already arriving in the other one, moved by the copy unit (cp.async.bulk -> UBLKCP) and signalled through an mbarrier:
+// no thread issues a load or a shared-memory store for the staging any more (the LDG -> STS variant below spent 18 % of its
+// stall samples on the STS waiting for its load and 25 % at the barrier behind it, profiles/r01_count_kernel_warp.md).
+// Warp 0 is the producer: lane s owns source s, keeps that source's header entries of the next two bins in registers, and
+// issues the copy of its segment. A coarse bin that does not fit a stage buffer takes the two-pass path from global memory.
+template <int R, int RF_THREADS, int RF_STAGE_BYTES>
+__global__ void __launch_bounds__(RF_THREADS) refine_bulk_kernel(RefineParams p) {
+  constexpr int W = R / 4;
+  constexpr int U = R / 16;
+  extern __shared__ __align__(128) uint8_t s_dyn[];
+  __shared__ uint32_t s_cnt[RF_MAX_SUB], s_cur[RF_MAX_SUB];
+  __shared__ const uint8_t *s_seg_ptr[2][kCountMaxSrc];
+  __shared__ uint32_t s_seg_start[2][kCountMaxSrc + 1];
+  __shared__ unsigned long long s_base[2];
+  __shared__ uint32_t s_warp[RF_THREADS / 32];
+  __shared__ __align__(8) uint64_t s_bar[2];
+  const int tid = threadIdx.x;
+  const uint32_t lane = tid & 31u, warp = tid >> 5;
+  const uint32_t F = 1u << p.fine_shift;
+  const uint32_t stage_cap = RF_STAGE_BYTES / R;
+  uint2 *fine_hdr = reinterpret_cast<uint2 *>(p.dst);
+  uint8_t *dst_rec = p.dst + p.dst_header_bytes;
+  uint8_t *stage[2] = {s_dyn, s_dyn + RF_STAGE_BYTES};
+
+  if (tid == 0) {
+    mbar_init(&s_bar[0], 1);
+    mbar_init(&s_bar[1], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  // producer state (warp 0): header entry of source `lane` (and lane + 32) for the bin about to be issued
+  const uint32_t c_first = p.coarse_begin + blockIdx.x, c_step = gridDim.x;
+  auto load_entry = [&](uint32_t c, int s) -> uint2 {
+    if (c >= p.coarse_end || s >= p.n_src) return make_uint2(0u, 0u);
+    const uint8_t *src = p.src_ptr[s];
+    return src ? reinterpret_cast<const uint2 *>(src)[c] : make_uint2(0u, 0u);
+  };
+  // issue the copies of coarse bin c into buffer b (warp 0, all lanes); e0 / e1 = this lane's entries for sources lane, lane + 32
+  auto issue = [&](uint32_t c, int b, uint2 e0, uint2 e1) {
+    const int s0 = (int)lane, s1 = (int)lane + 32;
+    const uint8_t *b0 = s0 < p.n_src ? p.src_ptr[s0] : nullptr, *b1 = s1 < p.n_src ? p.src_ptr[s1] : nullptr;
+    const uint32_t n0 = b0 ? e0.y : 0u, n1 = b1 ? e1.y : 0u;
+    // exclusive scan of the segment lengths over the sources (lanes, then the second set)
+    uint32_t i0 = n0, i1 = n1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t0 = __shfl_up_sync(0xffffffffu, i0, o), t1 = __shfl_up_sync(0xffffffffu, i1, o);
+      if ((int)lane >= o) i0 += t0, i1 += t1;
+    }
+    const uint32_t tot0 = __shfl_sync(0xffffffffu, i0, 31), tot1 = __shfl_sync(0xffffffffu, i1, 31);
+    const uint32_t st0 = i0 - n0, st1 = tot0 + i1 - n1, total = tot0 + tot1;
+    const uint8_t *p0 = b0 ? b0 + p.src_header_bytes + (uint64_t)e0.x * R : nullptr;
+    const uint8_t *p1 = b1 ? b1 + p.src_header_bytes + (uint64_t)e1.x * R : nullptr;
+    if (s0 < p.n_src) s_seg_ptr[b][s0] = p0, s_seg_start[b][s0] = st0;
+    if (s1 < p.n_src) s_seg_ptr[b][s1] = p1, s_seg_start[b][s1] = st1;
+    const bool staged = total <= stage_cap;
+    if (lane == 0) {
+      s_seg_start[b][p.n_src] = total;
+      s_base[b] = p.coarse_base[c];
+      mbar_arrive_expect_tx(&s_bar[b], staged ? total * (uint32_t)R : 0u);
+    }
+    __syncwarp();
+    if (staged) {
+      if (n0) bulk_load(stage[b] + (size_t)st0 * R, p0, n0 * (uint32_t)R, &s_bar[b]);
+      if (n1) bulk_load(stage[b] + (size_t)st1 * R, p1, n1 * (uint32_t)R, &s_bar[b]);
+    }
+  };
+
+  uint2 e_a0 = make_uint2(0u, 0u), e_a1 = e_a0, e_b0 = e_a0, e_b1 = e_a0;  // entries of the next bin to issue / the one after
+  if (warp == 0) {
+    e_a0 = load_entry(c_first, (int)lane), e_a1 = load_entry(c_first, (int)lane + 32);
+    e_b0 = load_entry(c_first + c_step, (int)lane), e_b1 = load_entry(c_first + c_step, (int)lane + 32);
+    if (c_first < p.coarse_end) issue(c_first, 0, e_a0, e_a1);
+  }
+  uint32_t it = 0;
+  for (uint32_t c = c_first; c < p.coarse_end; c += c_step, it++) {
+    const int b = (int)(it & 1u);
+    if (warp == 0) {
+      // the next bin of this CTA goes into the other buffer (everybody left it at the barrier that ended the last round)
+      const uint32_t cn = c + c_step;
+      const uint2 n0 = e_b0, n1 = e_b1;
+      e_b0 = load_entry(cn + c_step, (int)lane), e_b1 = load_entry(cn + c_step, (int)lane + 32);
+      if (cn < p.coarse_end) issue(cn, b ^ 1, n0, n1);
+    }
+    if (tid < RF_MAX_SUB) s_cnt[tid] = 0;
+    __syncthreads();  // s_cnt cleared; (first round) the producer's shared state of buffer b is visible
+    const uint32_t n = s_seg_start[b][p.n_src];
+    const unsigned long long base = s_base[b];
+    const bool staged = n <= stage_cap;
+    mbar_wait(&s_bar[b], (it >> 1) & 1u);
+    const uint32_t *st = reinterpret_cast<const uint32_t *>(stage[b]);
+    // ---- pass 1: histogram of the sub-bin ids
+    if (staged) {
+      for (uint32_t r = tid; r < n; r += RF_THREADS) atomicAdd(&s_cnt[(st[r * W + W - 1] >> 8) & (F - 1u)], 1u);
+    } else {
+      for (uint32_t r = tid; r < n; r += RF_THREADS) {
+        int s = 0;
+        while (s_seg_start[b][s + 1] <= r) s++;
+        const uint32_t w = reinterpret_cast<const uint32_t *>(s_seg_ptr[b][s] + (uint64_t)(r - s_seg_start[b][s]) * R)[W - 1];
+        atomicAdd(&s_cnt[(w >> 8) & (F - 1u)], 1u);
+      }
+    }
+    __syncthreads();
+    // ---- exclusive scan over the F sub-bins (F <= 256 = one value per thread)
+    {
+      const uint32_t v = (uint32_t)tid < F ? s_cnt[tid] : 0u;
+      uint32_t incl = v;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+        if ((int)lane >= d) incl += t;
+      }
+      if (lane == 31) s_warp[warp] = incl;
+      __syncthreads();
+      uint32_t off = incl - v;
+      for (uint32_t w = 0; w < warp; w++) off += s_warp[w];
+      if ((uint32_t)tid < F) {
+        s_cur[tid] = off;
+        fine_hdr[((uint64_t)c << p.fine_shift) + tid] = make_uint2((uint32_t)(base + off), v);
+      }
+    }
+    __syncthreads();
+    // ---- pass 2: scatter the records to their fine bins
+    if (staged) {
+      const uint32_t n16 = n * U;
+      for (uint32_t u0 = 0; u0 < n16; u0 += RF_THREADS) {
+        const uint32_t u = u0 + tid;
+        const bool on = u < n16;
+        const uint32_t r = on ? u / U : 0u, part = u % U;
+        const uint32_t hdr = st[r * W + W - 1];
+        uint32_t pos = 0;
+        if (on && part == 0) pos = atomicAdd(&s_cur[(hdr >> 8) & (F - 1u)], 1u);
+        if (U > 1) pos = __shfl_sync(0xffffffffu, pos, (lane / U) * U);
+        if (on) st_stream16(dst_rec + (base + pos) * R + 16 * part, reinterpret_cast<const uint4 *>(stage[b])[u]);
+      }
+    } else {
+      for (uint32_t r = tid; r < n; r += RF_THREADS) {
+        int s = 0;
+        while (s_seg_start[b][s + 1] <= r) s++;
+        const uint4 *g = reinterpret_cast<const uint4 *>(s_seg_ptr[b][s] + (uint64_t)(r - s_seg_start[b][s]) * R);
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) v[u] = g[u];
+        const uint32_t pos = atomicAdd(&s_cur[(v[U - 1].w >> 8) & (F - 1u)], 1u);
+#pragma unroll
+        for (int u = 0; u < U; u++) st_stream16(dst_rec + (base + pos) * R + 16 * u, v[u]);
+      }
+    }
+    __syncthreads();  // buffer b and the histogram are free again
+  }
+}
+
 cudaError_t launch_refine_totals(const RefineParams &p, cudaStream_t s, uint64_t *launches) {
   refine_totals_kernel<<<(p.n_coarse + 255) / 256, 256, 0, s>>>(p);
   refine_scan_kernel<<<1, 1024, 0, s>>>(p);
   *launches += 2;
+  return cudaGetLastError();
+}
+
+// bulk-copy variant: two stage buffers per CTA
+template <int R, int THREADS, int STAGE>
+static cudaError_t launch_refine_bulk_shape(const RefineParams &p, int sm_count, int ctas_per_sm, cudaStream_t s) {
+  uint64_t grid = (uint64_t)sm_count * ctas_per_sm;
+  const uint32_t n_bins = p.coarse_end - p.coarse_begin;
+  if (grid > n_bins) grid = n_bins ? n_bins : 1;
+  cudaError_t e = cudaFuncSetAttribute(refine_bulk_kernel<R, THREADS, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * STAGE);
+  if (e != cudaSuccess) return e;
+  refine_bulk_kernel<R, THREADS, STAGE><<<(int)grid, THREADS, 2 * STAGE, s>>>(p);
   return cudaGetLastError();
 }
 
@@ -236,6 +431,14 @@ static cudaError_t launch_refine_shape(const RefineParams &p, int sm_count, int 
   if (e != cudaSuccess) return e;
   refine_kernel<R, THREADS, STAGE><<<(int)grid, THREADS, STAGE, s>>>(p);
   return cudaGetLastError();
+}
+
+// shapes of the bulk variant: stage buffer (x 2), threads, CTAs per SM
+static const int RB_STAGE_TINY = 44 * 1024, RB_STAGE_SMALL = 100 * 1024;
+template <int R>
+static cudaError_t launch_refine_bulk_r(const RefineParams &p, int sm_count, int shape, cudaStream_t s) {
+  if (shape >= 1) return launch_refine_bulk_shape<R, 512, RB_STAGE_SMALL>(p, sm_count, 1, s);
+  return launch_refine_bulk_shape<R, 256, RB_STAGE_TINY>(p, sm_count, 2, s);
 }
 
 template <int R>
@@ -255,6 +458,19 @@ cudaError_t launch_refine(const RefineParams &p_in, uint64_t avg_records, int sm
   int shape = want > (uint64_t)RF_STAGE_SMALL ? 2 : (want > (uint64_t)RF_STAGE_TINY ? 1 : 0);
   if (const char *e = getenv("KC_REFINE_SHAPE")) shape = atoi(e);  // (experiments)
   (*launches)++;
+  bool bulk = true;
+  if (const char *e = getenv("KC_REFINE_BULK")) bulk = atoi(e) != 0;  // (experiments: 0 = the LDG -> STS staging)
+  if (bulk) {
+    const int bshape = want > (uint64_t)RB_STAGE_TINY ? 1 : 0;
+    int bs = bshape;
+    if (const char *e = getenv("KC_REFINE_BULK_SHAPE")) bs = atoi(e);
+    switch (p.rec_bytes) {
+      case 16: return launch_refine_bulk_r<16>(p, sm_count, bs, s);
+      case 32: return launch_refine_bulk_r<32>(p, sm_count, bs, s);
+      case 64: return launch_refine_bulk_r<64>(p, sm_count, bs, s);
+    }
+    return cudaErrorInvalidValue;
+  }
   switch (p.rec_bytes) {
     case 16: return launch_refine_r<16>(p, sm_count, shape, s);
     case 32: return launch_refine_r<32>(p, sm_count, shape, s);
