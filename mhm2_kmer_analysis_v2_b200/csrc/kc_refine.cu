@@ -460,6 +460,7 @@ cudaError_t launch_refine(const RefineParams &p_in, uint64_t avg_records, int sm
   (*launches)++;
   bool bulk = true;
   if (const char *e = getenv("KC_REFINE_BULK")) bulk = atoi(e) != 0;  // (experiments: 0 = the LDG -> STS staging)
+  if (bulk && want > (uint64_t)RB_STAGE_SMALL && !getenv("KC_REFINE_BULK_SHAPE")) bulk = false;  // bins that need the 208 KB single stage
   if (bulk) {
     const int bshape = want > (uint64_t)RB_STAGE_TINY ? 1 : 0;
     int bs = bshape;

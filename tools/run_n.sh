@@ -2,7 +2,7 @@
 N=$1
 mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
-for X in pull copy; do
+for X in ${XMODES:-pull copy}; do
   echo "== exchange $X"
   timeout 600 $TR bench.py --gpus $N --exchange $X --configs none --no-e2e --steps 5 --warmup 3 > gpurun_out/r02_n${N}_$X.json 2> gpurun_out/r02_n${N}_$X.err
   echo "rc=$?"; tail -2 gpurun_out/r02_n${N}_$X.err
