@@ -820,7 +820,7 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="skip the untimed parity pass against the CPU checker")
     ap.add_argument("--parity-reads", type=int, default=400_000, help="reads (all ranks together) of the parity pass")
     ap.add_argument("--configs", default="auto", choices=["none", "auto", "all"], help="also measure the other BASELINE configs (reduced steps)")
-    ap.add_argument("--exchange", default="copy", choices=["pull", "copy", "nccl"],
+    ap.add_argument("--exchange", default="pull", choices=["pull", "copy", "nccl"],
                     help="multi-GPU: 'copy' = peers' bins mapped with CUDA IPC, copy engines move them slice by slice beside the refine / "
                          "count kernels; 'pull' = the refine kernel reads them over NVLink itself; 'nccl' = all-to-all of the owner "
                          "regions, then refine")

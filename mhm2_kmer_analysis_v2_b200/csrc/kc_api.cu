@@ -93,6 +93,8 @@ struct kc_ctx {
   cudaEvent_t ev_rs0[kSinkSlices], ev_rs1[kSinkSlices];  // refine slice i: start / end (refine_stream)
   cudaEvent_t ev_cs0[kSinkSlices], ev_cs1[kSinkSlices];  // count slice i: start / end (stream)
   int n_count_slices = 0, n_refine_slices = 0;
+  unsigned int *d_slice_done = nullptr;  // [kSlices] coarse bins refined per slice (SM-partitioned pipeline)
+  bool partitioned = false;              // the last insert ran refine and count side by side on disjoint SMs
   // copy-mode exchange (kc_exchange_set_mode(KC_XCHG_COPY)): copy engines move the peers' regions into d_recv
   int xmode = KC_XCHG_PULL;
   cudaStream_t xfer_stream[kXferStreams] = {nullptr, nullptr, nullptr, nullptr};
@@ -391,7 +393,12 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   CREATE_CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
   CREATE_CK(cudaStreamCreateWithFlags(&c->in_stream, cudaStreamNonBlocking));
   CREATE_CK(cudaStreamCreateWithFlags(&c->parse_stream2, cudaStreamNonBlocking));
-  CREATE_CK(cudaStreamCreateWithFlags(&c->refine_stream, cudaStreamNonBlocking));
+  {
+    // the refine kernel of the SM-partitioned pipeline must become resident before the count kernel that waits for it
+    int lo = 0, hi = 0;
+    CREATE_CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CREATE_CK(cudaStreamCreateWithPriority(&c->refine_stream, cudaStreamNonBlocking, hi));
+  }
   CREATE_CK(cudaEventCreate(&c->ev_fork));
   CREATE_CK(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
   for (auto &e2 : c->ev_slice) CREATE_CK(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
@@ -407,6 +414,7 @@ extern "C" int kc_create(const kc_config *cfg, kc_ctx **out) {
   CREATE_CK(cudaHostAlloc((void **)&c->h_pinned, kPinnedWords * sizeof(unsigned long long), cudaHostAllocDefault));
   CREATE_CK(dev_alloc(&c->d_ctr, 1));
   CREATE_CK(dev_alloc(&c->d_scratch, kScratchWords));
+  CREATE_CK(dev_alloc(&c->d_slice_done, kSlices + 1));
   CREATE_CK(cudaMemsetAsync(c->d_ctr, 0, sizeof(DevCounters), c->stream));
 #undef CREATE_CK
   configure_bins(c);
@@ -517,6 +525,7 @@ extern "C" void kc_destroy(kc_ctx *c) {
   if (c->h_slice_n) cudaFreeHost(c->h_slice_n);
   if (c->h_pinned) cudaFreeHost(c->h_pinned);
   dev_free(c->d_scratch);
+  dev_free(c->d_slice_done);
   dev_free(c->d_lq);
   dev_free(c->d_lc);
   dev_free(c->d_ll);
@@ -1293,6 +1302,19 @@ static int n_pipeline_slices(const kc_ctx *c) {
 // (the count CTAs hold all of its shared memory), so refine CTAs displace count CTAs and the pair takes 57.0 ms against
 // 51.7 ms back to back. With peers the refine kernel spends its time waiting for NVLink, and hiding that behind the count
 // pass wins.
+// SM-partitioned pipeline (G >= 4, no result sink): ONE refine launch on a few SMs of its own (one 1024-thread CTA with the
+// 208 KB stage each) pulls the peers' bins over NVLink for the whole insert phase while ONE count launch runs on all the
+// other SMs; the count warps wait on per-slice counters the refine kernel bumps (device-side, no host, no launch seams).
+// Why not slice-wise launches on two streams: a refine CTA needs a whole SM's shared memory and so do the count CTAs, so a
+// refine launch only gets SMs as the previous count launch drains -- measured at 8 GPUs the two passes simply added up
+// (refine 20 ms + count 45 ms = 65 ms insert).
+static int refine_partition_sms(const kc_ctx *c, bool to_sink) {
+  int sms = 0;
+  if (c->G >= 4 && c->fine_shift && !to_sink && c->xmode == KC_XCHG_PULL) sms = c->G >= 8 ? 24 : 20;
+  if (const char *e = getenv("KC_REFINE_SMS")) sms = atoi(e);  // (experiments; 0 = off)
+  if (sms < 0 || sms > c->sm_count / 2 || !c->fine_shift || to_sink) sms = 0;
+  return sms;
+}
 static bool refine_overlaps_count(const kc_ctx *c) {
   if (const char *e = getenv("KC_REFINE_OVERLAP")) return atoi(e) != 0;  // (experiments)
   return c->G > 1 && c->xmode == KC_XCHG_PULL;
@@ -1407,6 +1429,51 @@ static int launch_count_pipeline(kc_ctx *c, bool redo) {
     CK(cudaStreamWaitEvent(c->refine_stream, c->ev_fork, 0));
     if (copy)
       for (int q = 0; q < kXferStreams; q++) CK(cudaStreamWaitEvent(c->xfer_stream[q], c->ev_fork, 0));
+  }
+  const int part_sms = (refine && !redo) ? refine_partition_sms(c, to_sink) : 0;
+  c->partitioned = part_sms > 0;
+  if (part_sms > 0) {
+    CK(cudaMemsetAsync(c->d_slice_done, 0, (kSlices + 1) * sizeof(unsigned int), c->stream));
+    CK(cudaEventRecord(c->ev_fork, c->stream));
+    CK(cudaStreamWaitEvent(c->refine_stream, c->ev_fork, 0));
+    rp.n_src = c->G;
+    rp.rec_bytes = c->rec_bytes;
+    rp.n_coarse = (uint32_t)c->P;
+    rp.fine_shift = c->fine_shift;
+    rp.src_header_bytes = c->header_bytes;
+    rp.src_ptr = c->d_count_src;
+    rp.dst_header_bytes = fine_header_bytes(c);
+    rp.coarse_base = c->d_coarse_base;
+    rp.total = c->d_coarse_base + c->P + 1;
+    rp.err_too_large = &c->d_ctr->err_bins_full;
+    rp.dst = c->d_fine;
+    rp.n_slices = S;
+    rp.slice_done = c->d_slice_done;
+    rp.grid_limit = part_sms;
+    cp.wait_slices = S;
+    cp.slice_done = c->d_slice_done;
+    cp.err_wait = &c->d_ctr->err_wait;
+    for (int i = 0; i <= S; i++) {
+      rp.slice_coarse_edge[i] = slice_edge((uint32_t)c->P, i, S);
+      cp.slice_fine_edge[i] = rp.slice_coarse_edge[i] << c->fine_shift;
+      if (i) cp.slice_need[i - 1] = rp.slice_coarse_edge[i] - rp.slice_coarse_edge[i - 1];
+    }
+    CK(launch_refine_totals(rp, c->refine_stream, &c->launches));
+    CK(cudaEventRecord(c->ev_rs0[0], c->refine_stream));
+    CK(launch_refine(rp, record_bound(c) / std::max<uint64_t>(rp.n_coarse, 1), c->sm_count, c->refine_stream, &c->launches));
+    CK(cudaEventRecord(c->ev_rs1[0], c->refine_stream));
+    c->n_refine_slices = 1;
+    cp.bin_begin = 0;
+    cp.bin_end = cp.n_bins;
+    // the count kernel may only be launched once the refine CTAs sit on their SMs (it would take every SM otherwise)
+    CK(launch_gate(c->d_slice_done + kSlices, (unsigned int)std::min<uint64_t>((uint64_t)part_sms, rp.n_coarse), c->stream, &c->launches));
+    CK(cudaEventRecord(c->ev_cs0[0], c->stream));
+    CK(launch_count(cp, c->N, dedup, c->sm_count - part_sms, c->stream, &c->launches));
+    CK(cudaEventRecord(c->ev_cs1[0], c->stream));
+    c->n_count_slices = 1;
+    CK(cudaStreamWaitEvent(c->stream, c->ev_rs1[0], 0));
+    CK(cudaEventRecord(c->ev_ik1, c->stream));
+    return KC_OK;
   }
   if (refine && !redo) {
     rp.n_src = c->G;
@@ -1589,6 +1656,18 @@ static int finalize_resident(kc_ctx *c, kc_stats *stats) {
   c->stats.ms_table_clear = 0;
   c->stats.ms_finalize = 0;
   if (c->h_ctr.err_bins_full) return fail(c, KC_ERR_ARG, "more than 2^32 supermer records for one rank; use more ranks");
+  if (c->h_ctr.err_wait) {
+    // SM-partitioned pipeline: count warps gave up waiting (the refine kernel was not resident beside them). The fine bins
+    // are complete by now (the refine stream was synchronised above): count them again, in the plain way.
+    if (getenv("KC_DEBUG")) fprintf(stderr, "[kc] partitioned pipeline: count warps timed out waiting for the refine kernel, recounting\n");
+    CK(cudaStreamSynchronize(c->copy_stream));
+    int rc = launch_count_pipeline(c, true);
+    if (rc) return rc;
+    c->stats.insert_kernel_launches++;
+    CK(cudaMemcpyAsync(&c->h_ctr, c->d_ctr, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    if (c->h_ctr.err_wait) return fail(c, KC_ERR_STATE, "finalize: count pass could not run");
+  }
   if (c->h_ctr.err_result_full) {
     // the dense result was under-sized: the counters hold the exact need, allocate that and count again
     CK(cudaEventRecord(c->ev0, c->stream));

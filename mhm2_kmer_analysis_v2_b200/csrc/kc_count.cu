@@ -277,8 +277,13 @@ __device__ __forceinline__ uint32_t stage_chunk(const CountParams &p, WarpCtx &w
 #pragma unroll
     for (int u = 0; u < U; u++) v[u] = make_uint4(0u, 0u, 0u, 0u);
     if (valid && src) {
+      if (p.wait_slices) {  // the refine kernel is still writing elsewhere in this buffer: no non-coherent path
 #pragma unroll
-      for (int u = 0; u < U; u++) v[u] = ld_stream16(src + 16 * u);
+        for (int u = 0; u < U; u++) v[u] = ld_cg16(src + 16 * u);
+      } else {
+#pragma unroll
+        for (int u = 0; u < U; u++) v[u] = ld_stream16(src + 16 * u);
+      }
     }
     const uint32_t cnt = v[U - 1].w & 0xffu;
     const uint32_t m_nz = __ballot_sync(0xffffffffu, cnt != 0u);
@@ -479,26 +484,62 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
   const uint8_t *src0 = p.src0 ? p.src0 : (p.n_src == 1 ? p.src_ptr[0] : nullptr);
   const uint2 *hdr0 = reinterpret_cast<const uint2 *>(src0);
   const bool single = p.n_src == 1 && hdr0 != nullptr;
+  // SM-partitioned pipeline: fine bins below ready_end are known to be refined; a warp that gets past it waits for the
+  // next slice's counter (all lanes acquire it). An entry that may not be read yet is marked kNotYet and fetched at its turn.
+  const uint2 kNotYet = make_uint2(0u, 0xffffffffu);
+  uint32_t ready_end = p.wait_slices ? 0u : 0xffffffffu;
+  int next_slice = 0;
+  auto wait_for = [&](uint64_t b) {
+    while (b >= ready_end && next_slice < p.wait_slices) {
+      const uint32_t need = p.slice_need[next_slice];
+      if (lane == 0) {
+        // one poller per warp with a growing pause: thousands of warps wait on this one word, and the refine kernel's
+        // atomics have to get through to it (polling every 256 ns from every lane made the refine pass 100x slower)
+        uint32_t pause = 1000, spins = 0;
+        while (ld_acquire32(p.slice_done + next_slice) < need) {
+          __nanosleep(pause);
+          if (pause < 16000u) pause *= 2;
+          if (++spins > (1u << 18)) {  // seconds: the refine kernel is not running beside us
+            *p.err_wait = 1u;
+            break;
+          }
+        }
+      }
+      __syncwarp();
+      (void)ld_acquire32(p.slice_done + next_slice);  // every lane acquires what lane 0 saw
+      __syncwarp();
+      ready_end = p.slice_fine_edge[next_slice + 1];
+      next_slice++;
+    }
+  };
+  auto load_entry = [&](uint64_t b) -> uint2 { return p.wait_slices ? ld_cg_u2(hdr0 + b) : hdr0[b]; };
   uint2 e_pre1 = make_uint2(0u, 0u), e_pre2 = make_uint2(0u, 0u);
   {
     const uint64_t b0 = (uint64_t)p.bin_begin + blockIdx.x * CW_WARPS + warp;
-    if (single && b0 < p.bin_end) e_pre1 = hdr0[b0];
-    if (single && b0 + n_warps < p.bin_end) e_pre2 = hdr0[b0 + n_warps];
+    if (single && b0 < p.bin_end) {
+      wait_for(b0);
+      e_pre1 = load_entry(b0);
+    }
+    if (single && b0 + n_warps < p.bin_end) e_pre2 = b0 + n_warps < ready_end ? load_entry(b0 + n_warps) : kNotYet;
   }
   for (uint64_t bin64 = (uint64_t)p.bin_begin + blockIdx.x * CW_WARPS + warp; bin64 < p.bin_end; bin64 += n_warps) {
     const uint32_t bin = (uint32_t)bin64;
     // ---- the bin's segments: header entry {first record, n records} of every source region
     uint32_t total = 0;
     if (single) {
-      const uint2 e = e_pre1;
+      uint2 e = e_pre1;
+      if (e.y == kNotYet.y) {  // (the slice was not finished when this entry was due)
+        wait_for(bin64);
+        e = load_entry(bin64);
+      }
       e_pre1 = e_pre2;
-      {
+      if (e_pre1.y != kNotYet.y) {
         const uint8_t *nx = src0 + p.header_bytes + (uint64_t)e_pre1.x * R;
         const uint32_t n_lines = (e_pre1.y * R + 127u) >> 7;
         for (uint32_t l = lane; l < n_lines; l += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + (size_t)l * 128));
       }
       const uint64_t b2 = (uint64_t)bin + 2ull * n_warps;
-      e_pre2 = b2 < p.bin_end ? hdr0[b2] : make_uint2(0u, 0u);
+      e_pre2 = b2 < p.bin_end ? (b2 < ready_end ? load_entry(b2) : kNotYet) : make_uint2(0u, 0u);
       wc.seg_ptr[0] = src0 + p.header_bytes + (uint64_t)e.x * R;  // (every lane mirrors source 0)
       wc.seg_ptr[1] = nullptr;
       wc.seg_n[0] = e.y;

@@ -202,6 +202,11 @@ __device__ __forceinline__ uint64_t ld_cg64(const void *p) {
   asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(r) : "l"(p) : "memory");
   return r;
 }
+__device__ __forceinline__ uint2 ld_cg_u2(const void *p) {
+  uint2 r;
+  asm volatile("ld.global.cg.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory");
+  return r;
+}
 __device__ __forceinline__ uint32_t ld_acquire32(const void *p) {
   uint32_t r;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(r) : "l"(p) : "memory");

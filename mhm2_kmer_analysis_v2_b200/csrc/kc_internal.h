@@ -62,6 +62,7 @@ struct DevCounters {  // device-resident, zeroed by kc_reset
   unsigned int err_result_full;     // bin-resident counting: the dense result arrays were too small (n_final / n_ext hold the need)
   unsigned int err_count_stack;     // bin-resident counting: a bin could not be split far enough
   unsigned int err_index;           // lookup index: an insert did not terminate
+  unsigned int err_wait;            // SM-partitioned pipeline: a count warp gave up waiting for the refine kernel
   unsigned long long split_passes;  // extra passes over bins whose distinct k-mers did not fit shared memory
   unsigned long long parse_counted, parse_records, parse_raw;
   unsigned int err_bins_full;
@@ -170,6 +171,7 @@ cudaError_t launch_checksum(const uint64_t *keys, const uint16_t *counts, const 
 // The default path: every local bin is small enough that the distinct k-mers of the bin fit a hash table in shared
 // memory; one WARP counts a bin there and emits the purged / extension-resolved entries straight to the dense result.
 static const int kCountMaxSrc = 64;    // source ranks per owner the count kernel can read from
+static const int kSlicesMax = 12;      // slices of the bin range (kSlices below)
 static const int kCountMaxHeavy = 8;   // keys with more than 65535 occurrences per (bin, split pass)
 
 struct CountParams {
@@ -193,6 +195,14 @@ struct CountParams {
   uint16_t *ext_counts, *ext_ext8;
   char *ext_left, *ext_right;
   uint64_t cap_ext;
+  // SM-partitioned pipeline (kc_api.cu): the refine kernel runs BESIDE this launch on its own SMs and announces every
+  // finished coarse bin in slice_done[slice]; a warp that reaches a fine bin of slice s first waits until
+  // slice_done[s] == slice_need[s]. wait_slices = 0: everything is in place (the usual launch).
+  int wait_slices;
+  const unsigned int *slice_done;
+  uint32_t slice_fine_edge[kSlicesMax + 1];  // first fine bin of every slice
+  uint32_t slice_need[kSlicesMax];           // coarse bins of every slice
+  unsigned int *err_wait;                    // set when a wait did not end (the refine kernel never became resident)
 };
 // slots that fit the shared-memory budget of one CTA for N key words
 uint32_t count_table_slots(int n_words, int rec_bytes, int k);
@@ -210,8 +220,15 @@ struct RefineParams {
   unsigned long long *coarse_base; // [n_coarse + 1] records per coarse bin -> exclusive prefix
   unsigned long long *total;       // out: records of this owner
   unsigned int *err_too_large;
+  // SM-partitioned pipeline: after a coarse bin is written, slice_done[slice of the bin] += 1 (release); n_slices = 0: off
+  int n_slices;
+  unsigned int *slice_done;
+  uint32_t slice_coarse_edge[kSlicesMax + 1];
+  int grid_limit;                  // > 0: at most this many CTAs (the SMs set aside for this kernel)
 };
 cudaError_t launch_refine_totals(const RefineParams &p, cudaStream_t s, uint64_t *launches);
+// slice_done[kSlicesMax] counts the resident CTAs of a partitioned refine launch; the gate holds a stream until `need` are
+cudaError_t launch_gate(const unsigned int *resident, unsigned int need, cudaStream_t s, uint64_t *launches);
 cudaError_t launch_refine(const RefineParams &p, uint64_t avg_records, int sm_count, cudaStream_t s, uint64_t *launches);
 
 // ---- lookup index over the finalized result (kc_lookup.cu)
@@ -241,7 +258,7 @@ static const int kHeaderAlign = 64;
 // ---- slices of the bin range: the receive copies, the refine pass, the count pass and the result hand-off all work slice
 // by slice so that they overlap (kc_api.cu). Edge i of kSlices slices over n bins; the first two slices are small (1/48 and
 // 1/24 of the bins) so that the pipeline fills quickly, the rest are equal. The same function on every rank.
-static const int kSlices = 12;
+static const int kSlices = kSlicesMax;
 __host__ __device__ inline uint32_t slice_edge(uint32_t n, int i, int n_slices) {
   if (i <= 0) return 0u;
   if (i >= n_slices) return n;

@@ -92,6 +92,20 @@ __global__ void __launch_bounds__(1024) refine_scan_kernel(RefineParams p) {
   }
 }
 
+
+// SM-partitioned pipeline: every thread's writes of coarse bin c are made visible device-wide, then one thread counts the
+// bin into its slice (the count kernel, running beside this one, acquires the counter before it touches the slice)
+__device__ __forceinline__ void announce_bin(const RefineParams &p, uint32_t c) {
+  if (p.n_slices == 0) return;
+  __syncthreads();  // every thread's stores of this bin happen before thread 0's fence + atomic (cumulative release)
+  if (threadIdx.x == 0) {
+    int sl = 0;
+    while (sl + 1 < p.n_slices && c >= p.slice_coarse_edge[sl + 1]) sl++;
+    __threadfence();
+    atomicAdd(&p.slice_done[sl], 1u);
+  }
+}
+
 // ---- step B
 template <int R, int RF_THREADS, int RF_STAGE_BYTES>
 __global__ void __launch_bounds__(RF_THREADS) refine_kernel(RefineParams p) {
@@ -108,6 +122,7 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(RefineParams p) {
   const uint32_t stage_cap = RF_STAGE_BYTES / R;
   uint2 *fine_hdr = reinterpret_cast<uint2 *>(p.dst);
   uint8_t *dst_rec = p.dst + p.dst_header_bytes;
+  if (p.n_slices && tid == 0) atomicAdd(p.slice_done + kSlicesMax, 1u);  // "this CTA is resident" (gate_kernel)
 
   for (uint32_t c = p.coarse_begin + blockIdx.x; c < p.coarse_end; c += gridDim.x) {
     __syncthreads();  // the previous coarse bin is done with the shared state
@@ -217,6 +232,7 @@ __global__ void __launch_bounds__(RF_THREADS) refine_kernel(RefineParams p) {
         for (int u = 0; u < U; u++) st_stream16(dst_rec + (base + pos) * R + 16 * u, v[u]);
       }
     }
+    announce_bin(p, c);
   }
 }
 
@@ -274,6 +290,7 @@ __global__ void __launch_bounds__(RF_THREADS) refine_bulk_kernel(RefineParams p)
   uint8_t *dst_rec = p.dst + p.dst_header_bytes;
   uint8_t *stage[2] = {s_dyn, s_dyn + RF_STAGE_BYTES};
 
+  if (p.n_slices && tid == 0) atomicAdd(p.slice_done + kSlicesMax, 1u);  // "this CTA is resident" (gate_kernel)
   if (tid == 0) {
     mbar_init(&s_bar[0], 1);
     mbar_init(&s_bar[1], 1);
@@ -399,8 +416,26 @@ __global__ void __launch_bounds__(RF_THREADS) refine_bulk_kernel(RefineParams p)
         for (int u = 0; u < U; u++) st_stream16(dst_rec + (base + pos) * R + 16 * u, v[u]);
       }
     }
+    announce_bin(p, c);
     __syncthreads();  // buffer b and the histogram are free again
   }
+}
+
+// SM-partitioned pipeline: holds the stream it runs on until `need` CTAs of the refine kernel (launched on another stream)
+// are resident -- the count kernel queued behind it would otherwise fill every SM first and wait for a kernel that cannot
+// start. One warp, no shared memory: it takes nothing a refine CTA needs. Gives up after ~1 s (the count kernel's own
+// time-out and the recount in kc_finalize then keep the result right).
+__global__ void gate_kernel(const unsigned int *resident, unsigned int need) {
+  if (threadIdx.x != 0) return;
+  for (uint32_t spins = 0; spins < (1u << 20); spins++) {
+    if (ld_acquire32(resident) >= need) return;
+    __nanosleep(1000);
+  }
+}
+cudaError_t launch_gate(const unsigned int *resident, unsigned int need, cudaStream_t s, uint64_t *launches) {
+  (*launches)++;
+  gate_kernel<<<1, 32, 0, s>>>(resident, need);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_refine_totals(const RefineParams &p, cudaStream_t s, uint64_t *launches) {
@@ -416,6 +451,7 @@ static cudaError_t launch_refine_bulk_shape(const RefineParams &p, int sm_count,
   uint64_t grid = (uint64_t)sm_count * ctas_per_sm;
   const uint32_t n_bins = p.coarse_end - p.coarse_begin;
   if (grid > n_bins) grid = n_bins ? n_bins : 1;
+  if (p.grid_limit > 0 && grid > (uint64_t)p.grid_limit) grid = p.grid_limit;
   cudaError_t e = cudaFuncSetAttribute(refine_bulk_kernel<R, THREADS, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * STAGE);
   if (e != cudaSuccess) return e;
   refine_bulk_kernel<R, THREADS, STAGE><<<(int)grid, THREADS, 2 * STAGE, s>>>(p);
@@ -427,6 +463,7 @@ static cudaError_t launch_refine_shape(const RefineParams &p, int sm_count, int 
   uint64_t grid = (uint64_t)sm_count * ctas_per_sm;
   const uint32_t n_bins = p.coarse_end - p.coarse_begin;
   if (grid > n_bins) grid = n_bins ? n_bins : 1;
+  if (p.grid_limit > 0 && grid > (uint64_t)p.grid_limit) grid = p.grid_limit;
   cudaError_t e = cudaFuncSetAttribute(refine_kernel<R, THREADS, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, STAGE);
   if (e != cudaSuccess) return e;
   refine_kernel<R, THREADS, STAGE><<<(int)grid, THREADS, STAGE, s>>>(p);
@@ -459,6 +496,10 @@ cudaError_t launch_refine(const RefineParams &p_in, uint64_t avg_records, int sm
   if (const char *e = getenv("KC_REFINE_SHAPE")) shape = atoi(e);  // (experiments)
   (*launches)++;
   bool bulk = true;
+  if (p.grid_limit > 0) {  // SM-partitioned pipeline: one CTA owns a whole SM (208 KB stage), the count kernel has the others
+    shape = 2;
+    bulk = false;
+  }
   if (const char *e = getenv("KC_REFINE_BULK")) bulk = atoi(e) != 0;  // (experiments: 0 = the LDG -> STS staging)
   if (bulk && want > (uint64_t)RB_STAGE_SMALL && !getenv("KC_REFINE_BULK_SHAPE")) bulk = false;  // bins that need the 208 KB single stage
   if (bulk) {
