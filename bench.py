@@ -821,9 +821,9 @@ def main():
     ap.add_argument("--parity-reads", type=int, default=400_000, help="reads (all ranks together) of the parity pass")
     ap.add_argument("--configs", default="auto", choices=["none", "auto", "all"], help="also measure the other BASELINE configs (reduced steps)")
     ap.add_argument("--exchange", default="pull", choices=["pull", "copy", "nccl"],
-                    help="multi-GPU: 'copy' = peers' bins mapped with CUDA IPC, copy engines move them slice by slice beside the refine / "
-                         "count kernels; 'pull' = the refine kernel reads them over NVLink itself; 'nccl' = all-to-all of the owner "
-                         "regions, then refine")
+                    help="multi-GPU: 'pull' = peers' bins mapped with CUDA IPC, the refine kernel reads them over NVLink (>= 4 GPUs: on SMs "
+                         "of its own beside the count kernel); 'copy' = copy engines move them slice by slice; 'nccl' = all-to-all of "
+                         "the owner regions, then refine")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         print(f"note: warmup {args.warmup} < 3 (timing rules ask for >= 3)", file=sys.stderr)

@@ -1302,16 +1302,19 @@ static int n_pipeline_slices(const kc_ctx *c) {
 // (the count CTAs hold all of its shared memory), so refine CTAs displace count CTAs and the pair takes 57.0 ms against
 // 51.7 ms back to back. With peers the refine kernel spends its time waiting for NVLink, and hiding that behind the count
 // pass wins.
-// SM-partitioned pipeline (G >= 4, no result sink): ONE refine launch on a few SMs of its own (one 1024-thread CTA with the
-// 208 KB stage each) pulls the peers' bins over NVLink for the whole insert phase while ONE count launch runs on all the
-// other SMs; the count warps wait on per-slice counters the refine kernel bumps (device-side, no host, no launch seams).
-// Why not slice-wise launches on two streams: a refine CTA needs a whole SM's shared memory and so do the count CTAs, so a
-// refine launch only gets SMs as the previous count launch drains -- measured at 8 GPUs the two passes simply added up
-// (refine 20 ms + count 45 ms = 65 ms insert).
+// SM-partitioned pipeline (experimental, KC_REFINE_SMS=n): ONE refine launch on n SMs of its own (one 1024-thread CTA with
+// the 208 KB stage each) pulls the peers' bins over NVLink for the whole insert phase while ONE count launch runs on all the
+// other SMs; the count warps wait on per-slice counters the refine kernel bumps (device-side, no host, no launch seams), a
+// gate kernel holds the count launch back until the refine CTAs are resident.
+// Why it exists: a refine CTA needs a whole SM's shared memory and so do the count CTAs, so slice-wise launches on two
+// streams never co-reside -- at 8 GPUs the two passes simply add up (refine + pull ~20 ms + count ~45 ms = 65 ms insert).
+// Why it is off: measured at 8 GPUs (C2), 24 SMs: 132 ms per step, 36 SMs: 99.9 ms, off: 90.4 ms. One CTA moves one 113 KB
+// coarse bin at a time with barriers between load, histogram and scatter: ~20 us per bin over NVLink = 5.7 GB/s per SM,
+// so the refine pass on few SMs (66-98 ms) is slower than the count pass it was meant to hide behind. It needs a pull
+// that keeps many bulk copies in flight per SM.
 static int refine_partition_sms(const kc_ctx *c, bool to_sink) {
   int sms = 0;
-  if (c->G >= 4 && c->fine_shift && !to_sink && c->xmode == KC_XCHG_PULL) sms = c->G >= 8 ? 24 : 20;
-  if (const char *e = getenv("KC_REFINE_SMS")) sms = atoi(e);  // (experiments; 0 = off)
+  if (const char *e = getenv("KC_REFINE_SMS")) sms = atoi(e);
   if (sms < 0 || sms > c->sm_count / 2 || !c->fine_shift || to_sink) sms = 0;
   return sms;
 }

@@ -165,3 +165,23 @@ def test_packed_reads_container_as_input(oracle_mod, k, block):
     assert_same(st.result(True), o.result(True), f"packed reads k={k}")
     assert st.checksum(False) == o.checksum(False)
     st.close()
+
+
+@pytest.mark.parametrize("k,sms", [(33, 16), (77, 40)])
+def test_sm_partitioned_pipeline(oracle_mod, monkeypatch, k, sms):
+    """The insert pipeline of >= 4 ranks: ONE refine launch on `sms` SMs of its own beside ONE count launch on
+    the others, the count warps waiting on the per-slice counters the refine kernel bumps. Forced here on one GPU
+    (KC_REFINE_SMS); same table as the oracle's, pass after pass."""
+    monkeypatch.setenv("KC_REFINE_SMS", str(sms))
+    reads = K.generate(None, 60_000, seed=1200 + k, n_genomes=4, genome_len_min=100_000, genome_len_max=200_000, abundance_sigma=1.0,
+                       sub_rate=0.005)
+    o = oracle_run(oracle_mod, reads, k)
+    st = K.KcountStage(k, keep_ext_counts=True, local_bins=200_000)
+    st.add_reads(reads)
+    for _ in range(3):
+        st.reset()
+        stats = st.run()
+        assert stats["local_bins"] >= 65536 and stats["pipeline_slices"] == 1
+        assert st.checksum(True) == o.checksum(True) and st.checksum(False) == o.checksum(False)
+    assert_same(st.result(True), o.result(True), f"partitioned k={k}")
+    st.close()
