@@ -1,9 +1,6 @@
 # ncu captures of this round (one GPU): launch list of the default bench command, then --set full of the dominant kernels
 mkdir -p gpurun_out
 B="python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline --no-lookup --no-parity --configs none"
-$B > gpurun_out/r02_prof_plain.json 2>gpurun_out/r02_prof_plain.err && \
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r02_ncu_launches.csv $B > gpurun_out/r02_ncu_launches.log 2>&1
-echo "launch list rc=$?"
 P="--steps 1 --warmup 0 --no-e2e --no-cpu-baseline --no-lookup --no-parity --configs none --reads-per-gpu 4000000 --n-genomes 20"
 for K in 33 21 77; do
   python bench.py $P --k $K > gpurun_out/r02_prof_k$K.json 2>/dev/null && \
