@@ -172,6 +172,7 @@ __device__ __forceinline__ void probe_warp(const Table<N> &tb, const uint64_t (&
     uint4 v[ILP];
 #pragma unroll
     for (int u = 0; u < ILP; u++) v[u] = lds_volatile16(tb.tag + 4 * b[u]);  // (lanes that are done re-read their last bucket: harmless)
+    __syncwarp();  // every tag load of this round precedes every claim of this round -- by the programming model, not by luck
     // ---- lookups
 #pragma unroll
     for (int u = 0; u < ILP; u++) {

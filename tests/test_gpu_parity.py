@@ -185,3 +185,28 @@ def test_sm_partitioned_pipeline(oracle_mod, monkeypatch, k, sms):
         assert st.checksum(True) == o.checksum(True) and st.checksum(False) == o.checksum(False)
     assert_same(st.result(True), o.result(True), f"partitioned k={k}")
     st.close()
+
+
+def test_pinned_source_may_be_overwritten_after_sync(oracle_mod):
+    """include/kcount_b200.h: the source buffers of kc_add_reads "may be released or overwritten after kc_sync()". The copies
+    run asynchronously on the input stream when the source is pinned, so kc_sync has to wait for that stream as well."""
+    from mhm2_kmer_analysis_v2_b200.reads import PinnedBuffer
+
+    k = 33
+    reads = K.generate(None, 200_000, seed=77, **SMALL)
+    o = oracle_run(oracle_mod, reads, k)
+    n, nb = len(reads), len(reads.bytes)
+    pb, po, pl = PinnedBuffer(nb), PinnedBuffer(n * 8), PinnedBuffer(n * 2)
+    pb.array[:nb] = reads.bytes
+    po.view(np.uint64, n)[:] = reads.offsets
+    pl.view(np.uint16, n)[:] = reads.lens
+    st = K.KcountStage(k)
+    st.add_reads_ptr(pb.ptr.value, nb, po.ptr.value, pl.ptr.value, n)
+    st.sync()
+    pb.array[:nb] = 0xFF  # the caller reuses its buffers
+    po.view(np.uint64, n)[:] = 0
+    pl.view(np.uint16, n)[:] = 0
+    stats = st.run()
+    assert stats["counted_kmers"] == reads.counted_kmers(k)
+    assert st.checksum(False) == o.checksum(False)
+    st.close()
