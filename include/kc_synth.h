@@ -16,7 +16,7 @@ extern "C" {
 #endif
 
 /* status codes (the values of the like-named kc_status codes in kcount_b200.h) */
-enum { KC_SYNTH_OK = 0, KC_SYNTH_ERR_ARG = -1, KC_SYNTH_ERR_NOMEM = -3, KC_SYNTH_ERR_IO = -7 };
+enum { KC_SYNTH_OK = 0, KC_SYNTH_ERR_ARG = -1, KC_SYNTH_ERR_NOMEM = -3, KC_SYNTH_ERR_IO = -7, KC_SYNTH_ERR_FORMAT = -8 };
 
 typedef struct {
   uint64_t seed;
@@ -48,6 +48,20 @@ int kc_reads_save(const char *path, const uint8_t *bytes, uint64_t n_bytes, cons
  * Input of kc_add_packed_reads in tests and bench. Returns 0, -1 (argument) or -3 (arena too small). */
 int kc_reads_to_packed_layout(const uint8_t *bytes, const uint64_t *offsets, const uint16_t *lens, uint64_t n_reads, uint8_t *arena,
                               uint64_t arena_bytes, uint64_t block_bytes, uint64_t *headers, uint64_t *blocks_used);
+
+/* FASTQ (plain or gzip) -> PackedRead bytes + offsets + lens, the flat input of kc_add_reads. Follows
+ * FastqReader::get_next_fq_record (src/fastq.cpp:1028-1120: '@' name / sequence / '+' / qualities of equal length) and the
+ * PackedRead encoding (src/packed_reads.cpp:99-126). qual_offset 33 or 64; max_reads 0 = all. The arrays are malloc'ed:
+ * release them with kc_read_set_free. Pair merging / adapter trimming (src/merge_reads.cpp) is not done here. */
+typedef struct {
+  uint8_t *bytes;
+  uint64_t n_bytes;
+  uint64_t *offsets;
+  uint16_t *lens;
+  uint64_t n_reads;
+} kc_read_set;
+int kc_fastq_read(const char *path, int qual_offset, uint64_t max_reads, kc_read_set *out);
+void kc_read_set_free(kc_read_set *rs);
 
 #ifdef __cplusplus
 }

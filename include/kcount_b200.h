@@ -238,6 +238,9 @@ int kc_result_checksum(kc_ctx *ctx, int extended, uint64_t *checksum);
 /* Text dump, one "KMER count L R" line per survivor, sorted by key (kmer_dht.cpp:274-297 writes the same
  * lines unsorted and gzipped). extended adds the 8 counters. */
 int kc_dump_sorted(kc_ctx *ctx, const char *path, int extended);
+/* KmerDHT::dump_kmers as the reference writes it (src/kcount/kmer_dht.cpp:274-297): one "KMER count L R" line per survivor
+ * of this rank, in table order (unsorted), gzip-compressed when gz != 0 (the reference's kmers-<k>.txt.gz per rank). */
+int kc_dump_kmers(kc_ctx *ctx, const char *path, int gz);
 /* Batched lookup in the finalized result (replaces the point lookups KmerDHT::get_local_kmer_counts / kmer_exists /
  * get_kmer_count, src/kcount/kmer_dht.cpp:199-245, and the host map they search, kcount_gpu.cpp:439-471):
  * keys[n*N] canonical k-mers -> counts (0 = absent: purged, dropped as X / F, or never seen), L, R (0 when absent).

@@ -95,12 +95,18 @@ PROTOTYPES = {
     "kc_result_device_ptrs": (C.c_int, [vp, C.c_int, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
     "kc_result_checksum": (C.c_int, [vp, C.c_int, C.POINTER(C.c_uint64)]),
     "kc_dump_sorted": (C.c_int, [vp, C.c_char_p, C.c_int]),
+    "kc_dump_kmers": (C.c_int, [vp, C.c_char_p, C.c_int]),
     "kc_lookup": (C.c_int, [vp, vp, C.c_uint64, vp, vp, vp]),
     "kc_owner_of": (C.c_int, [vp, vp]),
     "kc_minimizer_len": (C.c_uint32, [vp]),
     "kc_host_alloc": (C.c_int, [C.POINTER(vp), C.c_size_t]),
     "kc_host_free": (C.c_int, [vp]),
 }
+
+class KcReadSet(C.Structure):
+    _fields_ = [("bytes", C.POINTER(C.c_uint8)), ("n_bytes", C.c_uint64), ("offsets", C.POINTER(C.c_uint64)), ("lens", C.POINTER(C.c_uint16)),
+                ("n_reads", C.c_uint64)]
+
 
 # every symbol include/kc_synth.h declares (libkc_synth.so: host-only C, no CUDA -- the CPU arms of bench.py load only this)
 SYNTH_PROTOTYPES = {
@@ -109,6 +115,8 @@ SYNTH_PROTOTYPES = {
     "kc_synth_destroy": (None, [vp]),
     "kc_synth_generate": (C.c_int, [vp, C.c_uint64, C.c_uint64, vp, vp, vp, C.POINTER(C.c_uint64), C.c_int]),
     "kc_reads_save": (C.c_int, [C.c_char_p, vp, C.c_uint64, vp, vp, C.c_uint64]),
+    "kc_fastq_read": (C.c_int, [C.c_char_p, C.c_int, C.c_uint64, C.POINTER(KcReadSet)]),
+    "kc_read_set_free": (None, [C.POINTER(KcReadSet)]),
     "kc_reads_to_packed_layout": (C.c_int, [vp, vp, vp, C.c_uint64, vp, C.c_uint64, C.c_uint64, vp, C.POINTER(C.c_uint64)]),
 }
 SYNTH_LIB_PATH = os.path.join(HERE, "libkc_synth.so")

@@ -13,6 +13,8 @@
 #include <thread>
 #include <vector>
 
+#include <zlib.h>
+
 #include "kc_internal.h"
 #include "kcount_b200.h"
 
@@ -2086,6 +2088,40 @@ extern "C" int kc_dump_sorted(kc_ctx *c, const char *path, int extended) {
   }
   fclose(f);
   return KC_OK;
+}
+
+// KmerDHT::dump_kmers (src/kcount/kmer_dht.cpp:274-297): the rank's survivors, one line each, in table order, gzipped
+extern "C" int kc_dump_kmers(kc_ctx *c, const char *path, int gz) {
+  ResultSet *r = pick(c, 0);
+  if (!r || !path) return fail(c, KC_ERR_STATE, "kc_dump_kmers: no result");
+  CK(cudaSetDevice(c->device));
+  HostResult h;
+  int rc = fetch(c, r, h, false);
+  if (rc) return rc;
+  gzFile zf = nullptr;
+  FILE *f = nullptr;
+  if (gz)
+    zf = gzopen(path, "wb");
+  else
+    f = fopen(path, "w");
+  if (!zf && !f) return fail(c, KC_ERR_IO, "cannot open %s", path);
+  std::string buf;
+  buf.reserve(1 << 20);
+  char s[KC_MAX_K + 1], tail[32];
+  bool ok = true;
+  for (uint64_t i = 0; i < r->n && ok; i++) {
+    key_to_string(&h.keys[i * c->N], c->k, s);
+    buf.append(s, c->k);
+    snprintf(tail, sizeof tail, " %u %c %c\n", h.counts[i], h.left[i], h.right[i]);  // kmer_dht.cpp:286
+    buf.append(tail);
+    if (buf.size() > (1u << 20) - 256 || i + 1 == r->n) {
+      ok = gz ? gzwrite(zf, buf.data(), (unsigned)buf.size()) == (int)buf.size() : fwrite(buf.data(), 1, buf.size(), f) == buf.size();
+      buf.clear();
+    }
+  }
+  if (gz) ok = gzclose(zf) == Z_OK && ok;
+  else ok = fclose(f) == 0 && ok;
+  return ok ? KC_OK : fail(c, KC_ERR_IO, "write to %s failed", path);
 }
 
 // KmerDHT::get_local_kmer_counts / kmer_exists / get_kmer_count (src/kcount/kmer_dht.cpp:199-245) as one batched call:

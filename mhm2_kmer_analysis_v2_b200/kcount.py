@@ -237,6 +237,10 @@ class KcountStage:
     def dump_sorted(self, path, extended=False):
         self._ck(self.L.kc_dump_sorted(self.h, os.fsencode(path), int(extended)))
 
+    def dump_kmers(self, path, gz=True):
+        """KmerDHT::dump_kmers (src/kcount/kmer_dht.cpp:274-297): `KMER count L R` per survivor, unordered, gzip-compressed."""
+        self._ck(self.L.kc_dump_kmers(self.h, os.fsencode(path), int(gz)))
+
     def lookup(self, keys):
         keys = np.ascontiguousarray(keys, np.uint64).reshape(-1, self.N)
         n = len(keys)
@@ -408,10 +412,15 @@ class KmerDHT:
     def clear_stores(self):
         pass
 
-    def dump_kmers(self, path=None):
-        """kmer_dht.cpp:274-297 writes `KMER count L R` lines per rank (gzipped, unordered); here: sorted, plain text."""
-        path = path or f"kmers-{self.kmer_len}.txt"
-        self.stage.dump_sorted(path, False)
+    def dump_kmers(self, path=None, sorted=False):
+        """kmer_dht.cpp:274-297: `KMER count L R` lines per rank, unordered, gzipped (`kmers-<k>.txt.gz`); sorted=True writes the
+        plain-text sorted dump the parity tests compare instead."""
+        if sorted:
+            path = path or f"kmers-{self.kmer_len}.txt"
+            self.stage.dump_sorted(path, False)
+        else:
+            path = path or f"kmers-{self.kmer_len}.txt.gz"
+            self.stage.dump_kmers(path, True)
         return path
 
     def local_kmers(self):

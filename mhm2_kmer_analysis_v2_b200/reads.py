@@ -44,6 +44,36 @@ class ReadSet:
             raise _lib.KcError(rc, f"kc_reads_save({path})")
 
     @staticmethod
+    def from_fastq(path, qual_offset=33, max_reads=0):
+        """FASTQ (plain or .gz) -> ReadSet, as FastqReader + the PackedRead constructor do (src/fastq.cpp:1028-1120,
+        src/packed_reads.cpp:99-126). Mates stay independent reads (no merging)."""
+        L = _lib.synth_lib()
+        rs = _lib.KcReadSet()
+        rc = L.kc_fastq_read(os.fsencode(path), qual_offset, max_reads, C.byref(rs))
+        if rc:
+            raise _lib.KcError(rc, f"kc_fastq_read({path})")
+        try:
+            n, nb = rs.n_reads, rs.n_bytes
+            b = np.ctypeslib.as_array(rs.bytes, shape=(nb,)).copy() if nb else np.zeros(0, np.uint8)
+            o = np.ctypeslib.as_array(rs.offsets, shape=(n,)).copy() if n else np.zeros(0, np.uint64)
+            ln = np.ctypeslib.as_array(rs.lens, shape=(n,)).copy() if n else np.zeros(0, np.uint16)
+        finally:
+            L.kc_read_set_free(C.byref(rs))
+        return ReadSet(b, o, ln)
+
+    def to_fastq(self, path, qual_offset=33):
+        """Writes the reads back as FASTQ (tests, examples): names @r<i>/1, bases ACGTN, qualities offset + the stored 5 bits."""
+        import gzip
+
+        opener = gzip.open if str(path).endswith(".gz") else open
+        with opener(path, "wt") as f:
+            for i in range(len(self)):
+                b = self.bytes[int(self.offsets[i]):int(self.offsets[i]) + int(self.lens[i])]
+                seq = "".join("ACGTNNNN"[x & 7] for x in b)
+                q = "".join(chr(qual_offset + (x >> 3)) for x in b)
+                f.write(f"@r{i}/1\n{seq}\n+\n{q}\n")
+
+    @staticmethod
     def from_strings(seqs, quals=None, qual_offset=33):
         """Build a ReadSet from ACGTN strings (+ optional quality strings), as PackedRead's constructor does."""
         code = {c: i for i, c in enumerate("ACGT")}
