@@ -557,11 +557,11 @@ def measure(K, env, args, spec, steps, warmup, headline):
                            "gbps_per_gpu_per_direction": pulled / xs / 1e9 if xs > 0 else None, "nvlink_peak_gbps": 900.0,
                            "nvlink_frac": pulled / xs / 1e9 / 900.0 if xs > 0 else None,
                            "owner_imbalance": red.get("owner_imbalance") if red else None}
+    rec["reference_pin"] = check_full_pin(spec, env, g, rec["checksum"])
     if not headline:
         st.close()
         free_reads(reads)
         return rec
-    rec["reference_pin"] = check_full_pin(spec, env, g, rec["checksum"])
 
     # ---- the transport north_star names literally, beside the default: same stage, NCCL all-to-all, 2 steps
     if env.world > 1 and args.exchange != "nccl":
@@ -866,6 +866,7 @@ def main():
                                "unique_kmers": r["table"]["unique_kmers"], "final_kmers": r["table"]["final_kmers"],
                                "table_bytes": r["table"]["table_bytes"], "filter_bytes": r["table"]["filter_bytes"],
                                "insert_passes": r["table"]["insert_passes"], "hbm_bytes_in_use": r["hbm_bytes_in_use"], "checksum": r["checksum"],
+                               "reference_pin_ok": r["reference_pin"]["ok"] if r.get("reference_pin") else None,
                                "exchange": r.get("exchange")}
             except SystemExit:
                 raise
