@@ -310,8 +310,25 @@ __device__ __forceinline__ uint32_t stage_chunk(const CountParams &p, WarpCtx &w
     rank0 += (uint32_t)__popc(m_nz);
   }
   n_nonempty = rank0;
+  if (lane == 0) wc.s_pre[rank0] = (uint16_t)run;  // (end marker: walk_chunk_split searches s_pre)
   __syncwarp();
   return run;
+}
+
+// part id of an occurrence inside a split bin (see "split passes" below): strand-invariant, from the centre of the k-mer
+template <int N, int R>
+__device__ __forceinline__ uint32_t part_id(const uint32_t *rec, int j, int k) {
+  // k-mer bases are record bases j + 1 .. j + k; pairs (j + 1 + i, j + k - i), the np = min(16, k / 2) innermost ones
+  const int h = k >> 1, np = h < 16 ? h : 16;
+  const int pl = j + 1 + h - np, pr = j + k - h + 1;  // first base of the left / right chunk
+  const uint32_t l0 = rec[pl >> 4], l1 = rec[min((pl >> 4) + 1, R / 4 - 1)];
+  const uint32_t r0 = rec[pr >> 4], r1 = rec[min((pr >> 4) + 1, R / 4 - 1)];
+  const uint32_t L = __funnelshift_l(l1, l0, (pl & 15) * 2), Rr = __funnelshift_l(r1, r0, (pr & 15) * 2);
+  // reverse the base order of the right chunk: bit reversal, then swap the two bits of every base back
+  uint32_t rv = __brev(Rr & (0xffffffffu << (32 - 2 * np)));  // np bases, now in the low bits, last base first
+  rv = ((rv >> 1) & 0x55555555u) | ((rv & 0x55555555u) << 1);
+  const uint32_t x = (L >> (32 - 2 * np)) ^ rv;
+  return (x * 0x9E3779B1u) >> 16;
 }
 
 // One staged chunk: all lanes walk its occurrences, 32 * ILP per step (lane l takes occurrences q0 + 32 u + l).
@@ -378,7 +395,8 @@ __device__ __forceinline__ void walk_chunk(const CountParams &p, const Table<N> 
       el[u] = sw ? (ra ^ 3u) : la;
       er[u] = sw ? (la ^ 3u) : ra;
       h[u] = count_hash<N>(key[u]);
-      mine[u] = active && (((uint32_t)(h[u] >> 48) & wc.split_mask) == wc.split_res);  // else: another part of a split bin
+      mine[u] = active;
+      if (wc.split_mask) mine[u] = active && ((part_id<N, R>(rec, j, k) & wc.split_mask) == wc.split_res);  // else: another part of a split bin
     }
     uint32_t slot[ILP];
     bool is_new[ILP], full = false;
@@ -416,6 +434,121 @@ __device__ __forceinline__ void walk_chunk(const CountParams &p, const Table<N> 
   __syncwarp();
 }
 
+// ---- split passes -----------------------------------------------------------------------------------------------
+// A bin whose distinct k-mers do not fit the table is counted in parts: part (split, res) takes the keys whose PART ID has
+// `res` in its low bits. Walking the bin once per part the ordinary way costs a full build + probe for every occurrence in
+// every pass -- p parts, p times the work (C3 at 100 x coverage, k = 55: 1.3 M split passes per GPU, the count pass 3.5 x
+// its unsplit time). Here a split pass is two stages:
+//   A. filter, ~1/8 of the work: the part id of occurrence q comes from the 32 bases around the CENTRE of the k-mer alone:
+//      XOR of the symmetric base pairs (b[c-1-i] ^ b[c+i]; complementing and reversing the k-mer maps every pair onto itself,
+//      so the id is the same on both strands and needs no canonical k-mer), mixed by one multiply. Occurrences of this part
+//      are appended to a 64-entry ring of occurrence numbers;
+//   B. whenever 32 are waiting, they are built and probed like an ordinary step -- with every lane busy.
+// so the build + probe work of a bin stays ~constant however many parts it needs. (The ring lives in the heavy-key side
+// table's shared memory, which is idle during a counting walk; the rare exact recount of keys beyond 65535 occurrences
+// walks the ordinary way, with the same part id.)
+template <int N, int R>
+__device__ __forceinline__ void walk_chunk_split(const CountParams &p, const Table<N> &tb, WarpCtx &wc, uint32_t total, uint32_t n_rank,
+                                                 uint32_t &claimed, bool &overflow) {
+  constexpr int W = R / 4;
+  constexpr int NBW = (R == 16 ? 32 : (R == 32 ? 80 : 160)) / 16;
+  const uint32_t lane = lane_id();
+  const uint32_t S = tb.n_slots;
+  const int k = p.k;
+  const int tail = 2 * (32 * N - k);
+  const uint64_t last_mask = ~0ULL << tail;
+  const int rw = (k + 1) >> 4;
+  const int rsh = 2 * (15 - ((k + 1) & 15));
+  const uint32_t le_mask = 0xffffffffu >> (31u - lane);
+  uint16_t *ring = reinterpret_cast<uint16_t *>(wc.s_heavy_side);  // 64 entries (the side table is 256 bytes)
+  uint32_t head = 0, waiting = 0, rank_run = 0;
+  const uint32_t n_steps = (total + 31u) >> 5;
+  for (uint32_t st = 0; st <= n_steps && !overflow; st++) {
+    if (st < n_steps) {
+      // ---- A: which occurrences of this step belong to the part
+      const uint32_t qb = st << 5, q = qb + lane;
+      const uint32_t bits = wc.s_bitmap[qb >> 5];
+      const bool active = q < total;
+      uint32_t rank = rank_run + (uint32_t)__popc(bits & le_mask) - 1u;
+      rank_run += (uint32_t)__popc(bits);
+      if (rank >= n_rank) rank = n_rank - 1u;
+      const uint32_t ri = wc.s_nz[rank];
+      const int j = active ? (int)(q - wc.s_pre[rank]) : 0;
+      const uint32_t pid = part_id<N, R>(wc.s_rec + ri * W, j, k);
+      const bool mine = active && ((pid & wc.split_mask) == wc.split_res);
+      const uint32_t m = __ballot_sync(0xffffffffu, mine);
+      if (mine) ring[(head + waiting + (uint32_t)__popc(m & ((1u << lane) - 1u))) & 63u] = (uint16_t)q;
+      waiting += (uint32_t)__popc(m);
+      __syncwarp();
+      if (waiting < 32u && st + 1 < n_steps) continue;
+    }
+    // ---- B: build and probe up to 32 waiting occurrences (everything that is left after the last step)
+    while (waiting && !overflow && (waiting >= 32u || st + 1 >= n_steps)) {
+      const uint32_t nb = min(waiting, 32u);
+      const bool active = lane < nb;
+      const uint32_t q = active ? ring[(head + lane) & 63u] : 0u;
+      head = (head + nb) & 63u;
+      waiting -= nb;
+      // record of occurrence q: last rank with s_pre[rank] <= q (s_pre[n_rank] = total)
+      uint32_t lo = 0, hi = n_rank;
+#pragma unroll
+      for (int it = 0; it < 7; it++) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (mid > lo && (uint32_t)wc.s_pre[mid] <= q) lo = mid;
+        else if (mid > lo) hi = mid;
+      }
+      const uint32_t ri = wc.s_nz[lo];
+      const int j = (int)(q - wc.s_pre[lo]);
+      const uint32_t *rec = wc.s_rec + ri * W;
+      // (the build below is walk_chunk's, for one occurrence per lane)
+      const int a = j >> 4, sft = (j & 15) * 2;
+      uint32_t wd[2 * N + 1];
+#pragma unroll
+      for (int i = 0; i < 2 * N; i++) wd[i] = rec[a + i];
+      wd[2 * N] = rec[min(a + 2 * N, W - 1)];
+      uint32_t x[2 * N + 1];
+#pragma unroll
+      for (int i = 0; i < 2 * N; i++) x[i] = __funnelshift_l(wd[i + 1], wd[i], sft);
+      x[2 * N] = wd[2 * N] << sft;
+      const uint32_t lb = x[0] >> 30;
+      const uint32_t rbw = rw == 2 * N - 2 ? x[2 * N - 2] : (rw == 2 * N - 1 ? x[2 * N - 1] : x[2 * N]);
+      const uint32_t rb = (rbw >> rsh) & 3u;
+      const uint32_t lq = (rec[NBW + (j >> 5)] >> (31 - (j & 31))) & 1u;
+      const int jr = j + k + 1;
+      const uint32_t rq = (rec[NBW + (jr >> 5)] >> (31 - (jr & 31))) & 1u;
+      uint64_t fw[N], rc[N];
+#pragma unroll
+      for (int i = 0; i < N; i++) {
+        const uint32_t hi32 = __funnelshift_l(x[2 * i + 1], x[2 * i], 2), lo32 = __funnelshift_l(x[2 * i + 2], x[2 * i + 1], 2);
+        fw[i] = ((uint64_t)hi32 << 32) | lo32;
+      }
+      fw[N - 1] &= last_mask;
+      revcomp_key<N>(fw, k, rc);
+      const bool sw = key_less<N>(rc, fw);
+      uint64_t key[1][N], h[1];
+#pragma unroll
+      for (int i = 0; i < N; i++) key[0][i] = sw ? rc[i] : fw[i];
+      const uint32_t la = lb | (lq << 2), ra = rb | (rq << 2);
+      const uint32_t el = sw ? (ra ^ 3u) : la, er = sw ? (la ^ 3u) : ra;
+      h[0] = count_hash<N>(key[0]);
+      bool mine[1] = {active};
+      uint32_t slot[1];
+      bool is_new[1], full = false;
+      probe_warp<N, true, 1>(tb, key, h, mine, slot, is_new, full);
+      if (slot[0] < C_PENDING) {
+        uint32_t *e = tb.ext + slot[0];
+        atomicAdd(tb.cnt + slot[0], 1u);
+        if (el & 4u) atomicAdd(e + ((el & 2u) ? S : 0u), 1u << ((el & 1u) << 4));
+        if (er & 4u) atomicAdd(e + ((er & 2u) ? 3u * S : 2u * S), 1u << ((er & 1u) << 4));
+      }
+      claimed += is_new[0];
+      if (__any_sync(0xffffffffu, full)) overflow = true;
+      __syncwarp();
+    }
+  }
+  __syncwarp();
+}
+
 // all records of the current bin, a chunk at a time
 template <int N, int R, bool HEAVY>
 __device__ __forceinline__ bool walk_bin(const CountParams &p, const Table<N> &tb, WarpCtx &wc, int cap_rec, uint32_t &claimed,
@@ -427,7 +560,10 @@ __device__ __forceinline__ bool walk_bin(const CountParams &p, const Table<N> &t
     const uint32_t occ = stage_chunk<R>(p, wc, c0, (int)min((uint32_t)cap_rec, total - c0), n_nz);
     n_records += n_nz;
     n_occ += occ;
-    if (occ) walk_chunk<N, R, HEAVY, (HEAVY ? 1 : CW_ILP)>(p, tb, wc, occ, n_nz, claimed, overflow);
+    if (occ) {
+      if (!HEAVY && wc.split_mask) walk_chunk_split<N, R>(p, tb, wc, occ, n_nz, claimed, overflow);
+      else walk_chunk<N, R, HEAVY, (HEAVY ? 1 : CW_ILP)>(p, tb, wc, occ, n_nz, claimed, overflow);
+    }
     // too full to go on efficiently (every lane counts its own claims)
     if (!HEAVY && !overflow && __reduce_add_sync(0xffffffffu, claimed) >= p.claim_limit) overflow = true;
   }
