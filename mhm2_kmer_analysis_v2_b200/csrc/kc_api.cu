@@ -47,6 +47,8 @@ struct ResultSet {
 };
 
 static const int kSinkSlices = kSlices;
+static const double kSampleMaxFrac = 0.2;   // default of KC_SAMPLE_MAX_FRAC (estimate_caps)
+static const double kPresplitFactor = 1.0;  // default of KC_PRESPLIT (count_params): the per-warp threshold starts at the host's estimate; 0 = bins are only split on overflow
 static_assert(KC_MAX_SLICES == kSlices, "the ABI's slice table and the pipeline disagree");
 static const int kXferStreams = 4;  // copy-engine streams of the copy-mode exchange (peers are dealt round-robin)
 static const int kPinnedWords = 4 * kCountMaxSrc + 64;  // pinned staging for small host <-> device parameter copies
@@ -902,6 +904,13 @@ static int estimate_caps(kc_ctx *c) {
     const double per_read = std::max(1.0, 2.0 * std::max(avg_len - c->k - 1, 0.0) / (double)(c->k - c->m + 2) + 1.0);
     const double per_bin = n > 400000u ? std::max(24.0, 64.0 * 400000.0 / (double)n) : 64.0;
     want_reads = std::max<uint64_t>(want_reads, (uint64_t)(per_bin * n / per_read));
+    // Long k: few records per read and many bins -- the rule above asks for half of the reads (k = 99: 10.9 M of 20 M, a sample
+    // pass of 11 ms in front of a 21 ms parse). Never look at more than this fraction of them; the margin of layout_caps_kernel
+    // widens with the thinner sample (more slack in the bin buffer, which is small for long k), and an overflow still falls
+    // back to the exact layout.
+    double max_frac = kSampleMaxFrac;
+    if (const char *e = getenv("KC_SAMPLE_MAX_FRAC")) max_frac = std::min(std::max(atof(e), 0.01), 1.0);  // (experiments)
+    want_reads = std::min<uint64_t>(want_reads, std::max<uint64_t>(262144, (uint64_t)(max_frac * (double)c->n_reads)));
   }
   // Which reads to look at: every stride-th read of all chunks -- or, when the input arrives in several chunks (a host
   // source is copied in sub-chunks), of the FIRST chunk only, so that the parse can start while the rest is still in
@@ -1388,6 +1397,28 @@ static CountParams count_params(kc_ctx *c) {
   cp.src0 = c->fine_shift ? c->d_fine : nullptr;
   cp.n_slots = c->count_slots;
   cp.claim_limit = (uint32_t)(0.85 * c->count_slots);
+  // pre-split threshold: records at which a bin's distinct k-mers are expected to pass the claim limit, from the k-mers per
+  // record this parse produced and the distinct / occurrence ratio of the sizing rule (configure_bins). KC_PRESPLIT scales
+  // it (0 = off).
+  cp.presplit_rec = 0;
+  {
+    double f = kPresplitFactor;
+    if (const char *e = getenv("KC_PRESPLIT")) f = atof(e);
+    const double depth = c->cfg.sequencing_depth > 0 ? c->cfg.sequencing_depth : 4;
+    const double kmer_err = 1.0 - std::pow(1.0 - c->cfg.base_error_rate, (double)c->k);
+    // Only where the sizing rule itself says that most distinct k-mers are error k-mers (long k): there the records of a bin
+    // predict its distinct k-mers. With short k a big bin is big because of coverage and the record count says little
+    // (measured on C2, k = 33: 1.2 % of the bins overflow, nothing to gain, 0.2-1 ms lost to needless splits).
+    const bool gate = getenv("KC_PRESPLIT") != nullptr || kmer_err * depth >= 1.0;
+    if (gate && f > 0.0 && c->stats.supermers_out > 0 && c->stats.counted_kmers > 0) {
+      const double r = 1.0 / depth + kmer_err;
+      const double occ_per_rec = (double)c->stats.counted_kmers / (double)c->stats.supermers_out;
+      const double lim = f * (double)cp.claim_limit / (r * occ_per_rec);
+      cp.presplit_rec = (uint32_t)std::min(std::max(lim, 2.0), 1e9);
+      cp.presplit_adapt = 1;
+      if (const char *e = getenv("KC_PRESPLIT_ADAPT")) cp.presplit_adapt = atoi(e) != 0;  // (experiments)
+    }
+  }
   cp.dmin_thres = c->cfg.dmin_thres;
   cp.keep_ext = keep_ext;
   cp.one_minus_dyn = 1.0 - c->cfg.dyn_min_depth;  // evaluated on the host exactly as the reference's constant expression

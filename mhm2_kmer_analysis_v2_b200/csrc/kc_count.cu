@@ -37,7 +37,7 @@ static const int CW_WARPS = 4;        // warps per CTA (independent of each othe
 static const int CW_THREADS = CW_WARPS * 32;
 static const int CW_CTAS_PER_SM = 5;  // 20 warps per SM (measured: 12 -> 54 ms, 16 -> 48, 20 -> 45.6, 24 -> 48.7 on C2; more warps hide latency, fewer mean larger tables and fewer bins)
 static const int CW_ILP = 1;          // k-mer occurrences per lane and step (independent instruction streams hide latency)
-static const int CW_STACK = 16;       // pending (split, residue) parts of a bin
+static const int CW_STACK = 24;       // pending (split, residue) parts of a bin: up to 8 to start with + one per doubling up to 32768
 static const int CW_TMAX = 3072;      // k-mer occurrences per staged chunk (bits of the record-start bitmap)
 static const uint32_t C_PENDING = 0xfffffffcu;
 static const uint32_t C_NOT_FOUND = 0xffffffffu;
@@ -659,6 +659,7 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
     }
     if (single && b0 + n_warps < p.bin_end) e_pre2 = b0 + n_warps < ready_end ? load_entry(b0 + n_warps) : kNotYet;
   }
+  float presplit_thr = (float)p.presplit_rec;  // records beyond which a bin starts out split (warp-uniform, adapts: see below)
   for (uint64_t bin64 = (uint64_t)p.bin_begin + blockIdx.x * CW_WARPS + warp; bin64 < p.bin_end; bin64 += n_warps) {
     const uint32_t bin = (uint32_t)bin64;
     // ---- the bin's segments: header entry {first record, n records} of every source region
@@ -712,8 +713,22 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
     }
     wc.n_rec = total;
     if (total == 0) continue;
-    int stack_n = 1;
-    if (lane == 0) wc.s_stack[0] = 1u << 16;  // (split << 16) | residue
+    // A bin with so many records that its distinct k-mers will not fit (p.presplit_rec: the host's estimate from the claim
+    // limit, the k-mers per record and the distinct / occurrence ratio) starts out split in 2, 4 or 8 parts instead of
+    // finding that out by a failed pass. Any split is exact; a wrong guess only costs time.
+    // The threshold is a per-warp estimate that corrects itself (the host's figure is only where it starts): the bins whose
+    // record count is NEAR it vote -- one that would have fit unsplit raises it by 2 %, one that would not lowers it by 4 % --
+    // so it settles where a bin of that size overflows one time in three: a failed pass of a long-k bin (full build + probe
+    // of most of its occurrences) costs about twice what a needless split does (staging, filter and sweep of the extra part;
+    // measured: with 4 % / 4 % the count pass of k = 77 took 79.0 ms against 75.9 ms with the host's threshold held fixed).
+    // Bins far above it that would have fit raise it too (a threshold that is far too low must not stay there).
+    uint32_t s0 = 1;
+    if (p.presplit_rec)
+      while (s0 < 8u && (float)total > (float)s0 * presplit_thr) s0 <<= 1;
+    uint32_t bin_unique = 0;
+    bool bin_overflowed = false;
+    int stack_n = (int)s0;
+    if (lane < s0) wc.s_stack[lane] = (s0 << 16) | (s0 - 1u - lane);  // (split << 16) | residue; residue 0 on top
     __syncwarp();
 
     // ---- parts of the bin: keys with hash bits & (split - 1) == residue; normally just (1, 0)
@@ -770,6 +785,7 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
         }
         __syncwarp();
         st_split += (lane == 0);
+        bin_overflowed = true;
         continue;
       }
       if (n_heavy) {
@@ -857,6 +873,7 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
       __syncwarp();
       clear_table<N>(tb);
       // the pass is complete: commit its statistics
+      if (p.presplit_adapt) bin_unique += __reduce_add_sync(0xffffffffu, ps.unique);
       st_unique += ps.unique;
       st_ge2 += ps.ge2;
       st_purged += ps.purged;
@@ -866,6 +883,12 @@ __global__ void __launch_bounds__(CW_THREADS, CW_CTAS_PER_SM) count_kernel(Count
         st_rec += nr;
         st_occ += no;
       }
+    }
+    if (p.presplit_adapt && (float)total > 0.75f * presplit_thr) {
+      // would the unsplit bin have overflowed? (a pre-split bin tells by its distinct k-mers, any other by what happened)
+      const bool would = s0 > 1u ? (bin_overflowed || bin_unique > p.claim_limit) : bin_overflowed;
+      if (!would) presplit_thr = fminf(presplit_thr * 1.02f, 1e9f);
+      else if ((float)total < 1.33f * presplit_thr) presplit_thr = fmaxf(presplit_thr * 0.96f, 2.0f);
     }
   }
 

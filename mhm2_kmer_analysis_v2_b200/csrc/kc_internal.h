@@ -184,6 +184,8 @@ struct CountParams {
   uint32_t n_slots;                  // table slots in shared memory (per warp)
   int warp_bytes;                    // shared memory of one warp (set by launch_count)
   uint32_t claim_limit;              // claimed slots at which a pass gives up and the bin is split further
+  int presplit_adapt;                // 1: every warp corrects the threshold from the bins it sees (kc_count.cu)
+  uint32_t presplit_rec;             // > 0: a bin with more than s x this many records starts out split in 2 s parts (s = 1, 2, 4)
   int dmin_thres, keep_ext;
   double one_minus_dyn;
   DevCounters *ctr;
