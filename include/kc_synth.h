@@ -63,6 +63,25 @@ typedef struct {
 int kc_fastq_read(const char *path, int qual_offset, uint64_t max_reads, kc_read_set *out);
 void kc_read_set_free(kc_read_set *rs);
 
+/* FASTQ -> mates as the pair loop of merge_reads() sees them (src/merge_reads.cpp:340-466), the input of the merge kernel
+ * (kc_merge_pairs / kc_add_read_pairs in kcount_b200.h): reads 2 i and 2 i + 1 are the mates of pair i, sequence and quality
+ * CHARACTERS as in the file (merging needs the full quality values, which the 5-bit PackedRead encoding drops). path2 = NULL:
+ * one interleaved file; path2 != NULL: mates alternate between the two files. paired = 0: an unpaired file -- every read gets
+ * the dummy mate "N" (quality = offset) that the reference gives it. Names are normalised as FastqReader::get_fq_name does
+ * (src/fastq.cpp:77-135: "/1" "/2", "-R1" "-R2", " 1:N:0:.." " 2:N:0:.."); a read 2 without its read 1 gets a faked "N" mate,
+ * and -- as in the reference -- a read 1 without its read 2 gets one too and ENDS the file (src/merge_reads.cpp:446-461: the
+ * end-of-file test looks at the already swapped-out name). Names that carry no pair marker are not supported. */
+typedef struct {
+  char *seq, *qual;
+  uint64_t n_bytes;
+  uint64_t *offsets;
+  uint16_t *lens;
+  uint64_t n_reads; /* 2 x pairs */
+  uint64_t missing_read1, missing_read2;
+} kc_pair_set;
+int kc_fastq_read_pairs(const char *path1, const char *path2, int paired, int qual_offset, uint64_t max_pairs, kc_pair_set *out);
+void kc_pair_set_free(kc_pair_set *ps);
+
 #ifdef __cplusplus
 }
 #endif

@@ -153,6 +153,34 @@ int kc_add_reads(kc_ctx *ctx, const uint8_t *bytes, uint64_t n_bytes, const uint
 int kc_add_packed_reads(kc_ctx *ctx, const void *headers, uint64_t n_reads, uint32_t header_stride);
 int kc_clear_reads(kc_ctx *ctx);
 
+/* ---- read-pair merging (the step in front of the k-mer analysis) -------------------------------------------------
+ * Replaces the pair loop of merge_reads() (src/merge_reads.cpp:466-650, called at src/main.cpp:210-215) and the PackedRead
+ * encoding of its output (src/packed_reads.cpp:99-126), on the GPU (kc_merge.cu). Input: the mates as kc_fastq_read_pairs
+ * (kc_synth.h) delivers them -- reads 2 i and 2 i + 1 are pair i, sequence and quality CHARACTERS, offsets[] / lens[] into
+ * seq / qual (n_bytes = their extent). Output, per pair and in input order: the merged read followed by the one-base dummy
+ * mate "N", or the two mates as they came (mate 1 with the qualities an N comparison zeroed, as in the reference); a pair of
+ * two mates shorter than min_kmer_len is dropped (paired != 0 only). No adapter trimming (src/adapters.cpp). Mates longer than
+ * KC_MERGE_MAX_READ_LEN are passed through unmerged and counted in too_long. Illegal base or quality characters: KC_ERR_ARG
+ * (the reference aborts). Host or device input pointers. */
+#define KC_MERGE_MAX_READ_LEN 512
+typedef struct {
+  uint64_t pairs, merged, ambiguous; /* "merged", "ambiguous" of the reference's summary (src/merge_reads.cpp:688-690) */
+  uint64_t merged_len, overlap_len;  /* sums over the merged pairs: average merged length / overlap length */
+  uint64_t max_read_len;             /* longest merged read */
+  uint64_t dropped_short, too_long;
+  uint64_t sum_read_lens;            /* the value merge_reads returns is sum_read_lens / (2 x pairs) */
+  uint64_t out_bytes;                /* extent of the output byte buffer = sum of all input lengths */
+  uint64_t launches;                 /* kernels launched */
+  double ms_kernel;
+} kc_merge_stats;
+/* host arrays out: out_bytes [n_bytes], out_offsets / out_lens [2 n_pairs]; *n_out_reads = reads written (2 per kept pair) */
+int kc_merge_pairs(int device, const char *seq, const char *qual, const uint64_t *offsets, const uint16_t *lens, uint64_t n_pairs,
+                   uint64_t n_bytes, int qual_offset, int min_kmer_len, int paired, uint8_t *out_bytes, uint64_t *out_offsets,
+                   uint16_t *out_lens, uint64_t *n_out_reads, kc_merge_stats *stats);
+/* the same, with the result appended to a stage context without leaving HBM (a dropped pair stays behind as two empty reads) */
+int kc_add_read_pairs(kc_ctx *ctx, const char *seq, const char *qual, const uint64_t *offsets, const uint16_t *lens, uint64_t n_pairs,
+                      uint64_t n_bytes, int qual_offset, int min_kmer_len, int paired, kc_merge_stats *stats);
+
 /* ---- the stage, phase by phase (all asynchronous on the context's stream unless noted) ----------- */
 /* (1)+(2) parse reads, extract minimizers, cut supermers, bin them per owner rank and local bin. */
 int kc_parse(kc_ctx *ctx);

@@ -5,4 +5,4 @@ and the reference-shaped KmerDHT / analyze_kmers), exchange.py (NCCL supermer al
 """
 from ._lib import KcError, build  # noqa: F401
 from .kcount import KcountStage, KmerDHT, KmerResult, PackedReads, analyze_kmers  # noqa: F401
-from .reads import CONFIGS, PackedReadsLayout, ReadSet, Synth, generate  # noqa: F401
+from .reads import CONFIGS, PackedReadsLayout, PairSet, ReadSet, Synth, generate, merge_pairs  # noqa: F401

@@ -97,11 +97,26 @@ PROTOTYPES = {
     "kc_dump_sorted": (C.c_int, [vp, C.c_char_p, C.c_int]),
     "kc_dump_kmers": (C.c_int, [vp, C.c_char_p, C.c_int]),
     "kc_lookup": (C.c_int, [vp, vp, C.c_uint64, vp, vp, vp]),
+    "kc_merge_pairs": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.POINTER(C.c_uint64), vp]),
+    "kc_add_read_pairs": (C.c_int, [vp, vp, vp, vp, vp, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, vp]),
     "kc_owner_of": (C.c_int, [vp, vp]),
     "kc_minimizer_len": (C.c_uint32, [vp]),
     "kc_host_alloc": (C.c_int, [C.POINTER(vp), C.c_size_t]),
     "kc_host_free": (C.c_int, [vp]),
 }
+
+class KcMergeStats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("pairs", "merged", "ambiguous", "merged_len", "overlap_len", "max_read_len", "dropped_short",
+                                          "too_long", "sum_read_lens", "out_bytes", "launches")] + [("ms_kernel", C.c_double)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class KcPairSet(C.Structure):
+    _fields_ = [("seq", C.POINTER(C.c_char)), ("qual", C.POINTER(C.c_char)), ("n_bytes", C.c_uint64), ("offsets", C.POINTER(C.c_uint64)),
+                ("lens", C.POINTER(C.c_uint16)), ("n_reads", C.c_uint64), ("missing_read1", C.c_uint64), ("missing_read2", C.c_uint64)]
+
 
 class KcReadSet(C.Structure):
     _fields_ = [("bytes", C.POINTER(C.c_uint8)), ("n_bytes", C.c_uint64), ("offsets", C.POINTER(C.c_uint64)), ("lens", C.POINTER(C.c_uint16)),
@@ -117,6 +132,8 @@ SYNTH_PROTOTYPES = {
     "kc_reads_save": (C.c_int, [C.c_char_p, vp, C.c_uint64, vp, vp, C.c_uint64]),
     "kc_fastq_read": (C.c_int, [C.c_char_p, C.c_int, C.c_uint64, C.POINTER(KcReadSet)]),
     "kc_read_set_free": (None, [C.POINTER(KcReadSet)]),
+    "kc_fastq_read_pairs": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_uint64, C.POINTER(KcPairSet)]),
+    "kc_pair_set_free": (None, [C.POINTER(KcPairSet)]),
     "kc_reads_to_packed_layout": (C.c_int, [vp, vp, vp, C.c_uint64, vp, C.c_uint64, C.c_uint64, vp, C.POINTER(C.c_uint64)]),
 }
 SYNTH_LIB_PATH = os.path.join(HERE, "libkc_synth.so")

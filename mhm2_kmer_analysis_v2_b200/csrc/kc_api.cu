@@ -562,6 +562,7 @@ extern "C" int kc_set_result_sink(kc_ctx *c, uint64_t *keys, uint16_t *counts, c
   return KC_OK;
 }
 
+int kc::ctx_device(const kc_ctx *c) { return c ? c->device : -1; }
 extern "C" uint32_t kc_key_words(const kc_ctx *c) { return c ? c->N : 0; }
 extern "C" uint32_t kc_minimizer_len(const kc_ctx *c) { return c ? c->m : 0; }
 

@@ -6,7 +6,9 @@
 
 #include "kc_device.cuh"
 
+struct kc_ctx;
 namespace kc {
+int ctx_device(const kc_ctx *c);  // the CUDA device of a context (kc_api.cu)
 
 // ---- hash table ---------------------------------------------------------------
 // One 32-byte, sector-aligned block per slot holds what an insert touches:

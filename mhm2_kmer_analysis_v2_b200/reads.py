@@ -99,6 +99,57 @@ class ReadSet:
         return ReadSet(bs, np.concatenate(offs), lens)
 
 
+class PairSet:
+    """Mates of read pairs as FASTQ characters (what merging needs: full quality values): reads 2 i and 2 i + 1 are pair i.
+    seq / qual are uint8 arrays of characters, offsets / lens index them. The input of merge_pairs()."""
+
+    def __init__(self, seq, qual, offsets, lens, missing_read1=0, missing_read2=0):
+        self.seq, self.qual, self.offsets, self.lens = seq, qual, offsets, lens
+        self.missing_read1, self.missing_read2 = missing_read1, missing_read2
+
+    def __len__(self):
+        return len(self.lens) // 2
+
+    @staticmethod
+    def from_fastq(path, path2=None, paired=True, qual_offset=33, max_pairs=0):
+        """kc_fastq_read_pairs: one interleaved file, two files of mates, or (paired=False) an unpaired file whose reads get the
+        reference's dummy mate "N" (src/merge_reads.cpp:340-466)."""
+        L = _lib.synth_lib()
+        ps = _lib.KcPairSet()
+        rc = L.kc_fastq_read_pairs(os.fsencode(path), os.fsencode(path2) if path2 else None, 1 if paired else 0, qual_offset, max_pairs,
+                                   C.byref(ps))
+        if rc:
+            raise _lib.KcError(rc, f"kc_fastq_read_pairs({path})")
+        try:
+            n, nb = ps.n_reads, ps.n_bytes
+            as_u8 = lambda p: np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nb,)).copy() if nb else np.zeros(0, np.uint8)
+            seq, qual = as_u8(ps.seq), as_u8(ps.qual)
+            o = np.ctypeslib.as_array(ps.offsets, shape=(n,)).copy() if n else np.zeros(0, np.uint64)
+            ln = np.ctypeslib.as_array(ps.lens, shape=(n,)).copy() if n else np.zeros(0, np.uint16)
+            return PairSet(seq, qual, o, ln, ps.missing_read1, ps.missing_read2)
+        finally:
+            L.kc_pair_set_free(C.byref(ps))
+
+
+def merge_pairs(pairs, qual_offset=33, min_kmer_len=21, paired=True, device=0):
+    """Read-pair merging on the GPU (kc_merge_pairs; replaces the pair loop of merge_reads(), src/merge_reads.cpp:466-650):
+    PairSet -> (ReadSet of the merged / unmerged reads in the PackedRead encoding, statistics). No CPU path."""
+    L = _lib.lib()
+    n = len(pairs)
+    out_b = np.zeros(max(len(pairs.seq), 1), np.uint8)
+    out_o = np.zeros(max(2 * n, 1), np.uint64)
+    out_l = np.zeros(max(2 * n, 1), np.uint16)
+    n_out = C.c_uint64()
+    st = _lib.KcMergeStats()
+    rc = L.kc_merge_pairs(device, pairs.seq.ctypes.data, pairs.qual.ctypes.data, pairs.offsets.ctypes.data, pairs.lens.ctypes.data, n,
+                          len(pairs.seq), qual_offset, min_kmer_len, 1 if paired else 0, out_b.ctypes.data, out_o.ctypes.data,
+                          out_l.ctypes.data, C.byref(n_out), C.byref(st))
+    if rc:
+        raise _lib.KcError(rc, "kc_merge_pairs")
+    k = n_out.value
+    return ReadSet(out_b, out_o[:k].copy(), out_l[:k].copy()), st.as_dict()
+
+
 class PackedReadsLayout:
     """A ReadSet laid out as the reference's PackedReads holds it in memory (src/packed_reads.hpp:68-79, 136): a contiguous
     array of 16-byte PackedRead headers (bit fields + pointer) and the read bytes bump-allocated in 4 MB blocks. The blocks

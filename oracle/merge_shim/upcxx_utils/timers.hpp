@@ -17,19 +17,21 @@ inline std::string get_basename(const std::string &fname) {
 }
 
 class BaseTimer {
-  std::chrono::time_point<std::chrono::high_resolution_clock> t0;
-  double elapsed = 0;
+  mutable std::chrono::time_point<std::chrono::high_resolution_clock> t0;
+  mutable double elapsed = 0;
 
  public:
   BaseTimer() = default;
   BaseTimer(const std::string &) {}
-  void start() { t0 = CLOCK_NOW(); }
-  void stop() { elapsed += std::chrono::duration<double>(CLOCK_NOW() - t0).count(); }
+  void start() const { t0 = CLOCK_NOW(); }
+  void stop() const { elapsed += std::chrono::duration<double>(CLOCK_NOW() - t0).count(); }
   double get_elapsed() const { return elapsed; }
   void inc_elapsed(double s) { elapsed += s; }
   void done() const {}
   void done_all() const {}
   void clear() { elapsed = 0; }
+  double get_elapsed_since_start() const { return std::chrono::duration<double>(CLOCK_NOW() - t0).count(); }
+  void done_all_async() const {}
 };
 
 class IntermittentTimer : public BaseTimer {
@@ -39,8 +41,10 @@ class IntermittentTimer : public BaseTimer {
 class AsyncTimer : public BaseTimer {
  public:
   AsyncTimer(const std::string & = "") {}
-  upcxx::future<> initiate_construct_reduction() { return {}; }
-  upcxx::future<> initiate_stop_reduction() { return {}; }
+  upcxx::future<> initiate_construct_reduction() const { return {}; }
+  upcxx::future<> initiate_start_reduction() const { return {}; }
+  upcxx::future<> initiate_stop_reduction() const { return {}; }
+  void report(const std::string & = "") const {}
 };
 class Timer : public BaseTimer {
  public:
@@ -96,6 +100,9 @@ struct PromiseReduce {
   upcxx::future<> fulfill() { return {}; }
 };
 struct Timings {
+  static void set_pending(upcxx::future<>) {}
+  static upcxx::future<> get_pending() { return {}; }
+  static void wait_pending() {}
   static PromiseReduce &get_promise_reduce() {
     static PromiseReduce pr;
     return pr;
