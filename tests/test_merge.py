@@ -1,0 +1,146 @@
+"""Read-pair merging: kc_fastq_read_pairs + the merge kernel against the REFERENCE's merge_reads().
+
+tests/golden/merge/* were written by tests/golden/make_merge_golden.py from oracle/_ref/merge_ref = the reference's unmodified
+src/merge_reads.cpp / fastq.cpp / packed_reads.cpp behind oracle/merge_shim. Bit-exact: every base and every 5-bit quality.
+  * CPU (not gpu): the kernel's per-pair arithmetic (csrc/kc_merge_core.cuh, the same source the device compiles) run by
+    tests/cpp/merge_core_host.cpp behind the product's pair reader -- holds the arithmetic and the reader to the goldens here;
+  * GPU: kc_merge_pairs / kc_add_read_pairs through the C ABI.
+"""
+import gzip
+import hashlib
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import mhm2_kmer_analysis_v2_b200 as K
+from mhm2_kmer_analysis_v2_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden", "merge")
+INDEX = json.load(open(os.path.join(GOLD, "index.json")))
+NAMES = sorted(INDEX)
+
+
+def expected(name):
+    return gzip.open(os.path.join(GOLD, f"{name}.expect.txt.gz"), "rb").read()
+
+
+def paths(name):
+    f = [os.path.join(GOLD, x) for x in INDEX[name]["files"]]
+    return f[0], (f[1] if len(f) > 1 else None)
+
+
+def as_text(reads, qual_offset):
+    out = []
+    for i in range(len(reads)):
+        b = reads.bytes[int(reads.offsets[i]):int(reads.offsets[i]) + int(reads.lens[i])]
+        out.append("".join("ACGTNNNN"[x & 7] for x in b))
+        out.append("".join(chr(qual_offset + (x >> 3)) for x in b))
+    return ("\n".join(out) + "\n").encode() if out else b""
+
+
+@pytest.fixture(scope="module")
+def host_tool(tmp_path_factory):
+    exe = str(tmp_path_factory.mktemp("merge") / "merge_core_host")
+    pkg = os.path.join(ROOT, "mhm2_kmer_analysis_v2_b200")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-o", exe, os.path.join(ROOT, "tests", "cpp", "merge_core_host.cpp"),
+                    "-L" + pkg, "-lkc_synth", "-Wl,-rpath," + pkg], check=True)
+    return exe
+
+
+def test_goldens_are_intact():
+    for n in NAMES:
+        assert hashlib.sha256(expected(n)).hexdigest() == INDEX[n]["sha256"], n
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_merge_arithmetic_on_host_equals_reference(name, host_tool, tmp_path):
+    e = INDEX[name]
+    p1, p2 = paths(name)
+    out = tmp_path / "o.txt"
+    subprocess.run([host_tool, str(e["qual_offset"]), str(e["min_kmer_len"]), "1" if e["paired"] else "0", str(out), p1] + ([p2] if p2 else []),
+                   check=True, stderr=subprocess.DEVNULL)
+    assert out.read_bytes() == expected(name)
+
+
+def test_pair_reader_details(tmp_path):
+    # unpaired file: every read gets the dummy mate N with quality = offset (src/merge_reads.cpp:352-371)
+    p = tmp_path / "u.fq"
+    p.write_text("@a\nACGT\n+\nIIII\n@b\nGG\n+\n#I\n")
+    ps = K.PairSet.from_fastq(str(p), paired=False)
+    assert len(ps) == 2 and list(ps.lens) == [4, 1, 2, 1]
+    assert bytes(ps.seq) == b"ACGTNGGN" and bytes(ps.qual) == b"IIII!#I!"
+    # a read 2 without its read 1 gets a faked N as mate 1 (src/merge_reads.cpp:410-423); names in three formats
+    p = tmp_path / "m.fq"
+    p.write_text("@x/1\nAAAA\n+\nIIII\n@x/2\nTTTT\n+\nIIII\n@y/2\nCCCC\n+\nIIII\n@z-R1\nGGGG\n+\nIIII\n@z-R2\nGGGA\n+\nIIII\n")
+    ps = K.PairSet.from_fastq(str(p))
+    assert ps.missing_read1 == 1 and len(ps) == 3
+    assert bytes(ps.seq) == b"AAAATTTT" + b"NCCCC" + b"GGGGGGGA" and list(ps.lens) == [4, 4, 1, 4, 4, 4]
+    # malformed record
+    p = tmp_path / "bad.fq"
+    p.write_text("@x/1\nAAAA\n+\nIII\n")
+    with pytest.raises(_lib.KcError):
+        K.PairSet.from_fastq(str(p))
+
+
+def test_merge_refuses_without_a_device():
+    if _lib.lib().kc_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    ps = K.PairSet.from_fastq(paths("basic")[0], max_pairs=4)
+    with pytest.raises(_lib.KcError) as ei:
+        K.merge_pairs(ps)
+    assert ei.value.code == _lib.KC_ERR_CUDA  # there is no CPU path
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", NAMES)
+def test_merge_kernel_equals_reference(name):
+    e = INDEX[name]
+    p1, p2 = paths(name)
+    ps = K.PairSet.from_fastq(p1, p2, paired=e["paired"], qual_offset=e["qual_offset"])
+    reads, st = K.merge_pairs(ps, qual_offset=e["qual_offset"], min_kmer_len=e["min_kmer_len"], paired=e["paired"])
+    assert as_text(reads, e["qual_offset"]) == expected(name)
+    assert len(reads) == e["reads"] and st["launches"] == 1 and st["too_long"] == 0
+    assert st["merged"] == e["merged_or_dummy_mates"]
+    if st["dropped_short"] == 0 and st["pairs"]:
+        assert st["sum_read_lens"] // (2 * st["pairs"]) == e["avg_read_len"]  # what merge_reads() returns
+
+
+@pytest.mark.gpu
+def test_merged_pairs_feed_the_stage_without_leaving_hbm():
+    """kc_add_read_pairs -> kc_run equals kc_merge_pairs -> kc_add_reads -> kc_run (and so the oracle on the merged reads)."""
+    import ctypes as C
+
+    e = INDEX["basic"]
+    ps = K.PairSet.from_fastq(paths("basic")[0])
+    reads, _ = K.merge_pairs(ps)
+    a = K.KcountStage(k=21)
+    a.add_reads(reads)
+    sa = a.run()
+    ca = a.checksum()
+    b = K.KcountStage(k=21)
+    st = _lib.KcMergeStats()
+    rc = b.L.kc_add_read_pairs(b.h, ps.seq.ctypes.data, ps.qual.ctypes.data, ps.offsets.ctypes.data, ps.lens.ctypes.data, len(ps), len(ps.seq),
+                               33, e["min_kmer_len"], 1, C.byref(st))
+    assert rc == 0 and st.merged == e["merged_or_dummy_mates"]
+    sb = b.run()
+    assert b.checksum() == ca and sb["final_kmers"] == sa["final_kmers"] and sb["counted_kmers"] == sa["counted_kmers"]
+    from oracle.oracle import Oracle  # the checker (tests only)
+
+    o = Oracle(k=21)
+    o.add_reads(reads.bytes, reads.offsets, reads.lens)
+    o.finalize()
+    assert o.checksum() == ca
+
+
+@pytest.mark.gpu
+def test_merge_rejects_bad_characters():
+    seq = np.frombuffer(b"ACGTACGTACGTACGTACGT" + b"ACGTAC!TACGTACGTACGT", np.uint8).copy()
+    qual = np.frombuffer(b"I" * 40, np.uint8).copy()
+    ps = K.PairSet(seq, qual, np.array([0, 20], np.uint64), np.array([20, 20], np.uint16))
+    with pytest.raises(_lib.KcError) as ei:
+        K.merge_pairs(ps)
+    assert ei.value.code == _lib.KC_ERR_ARG
