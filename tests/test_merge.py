@@ -128,9 +128,9 @@ def test_merged_pairs_feed_the_stage_without_leaving_hbm():
     assert rc == 0 and st.merged == e["merged_or_dummy_mates"]
     sb = b.run()
     assert b.checksum() == ca and sb["final_kmers"] == sa["final_kmers"] and sb["counted_kmers"] == sa["counted_kmers"]
-    from oracle.oracle import Oracle  # the checker (tests only)
+    import oracle as O  # the checker (tests only)
 
-    o = Oracle(k=21)
+    o = O.Oracle(k=21)
     o.add_reads(reads.bytes, reads.offsets, reads.lens)
     o.finalize()
     assert o.checksum() == ca
@@ -138,9 +138,9 @@ def test_merged_pairs_feed_the_stage_without_leaving_hbm():
 
 @pytest.mark.gpu
 def test_merge_rejects_bad_characters():
-    seq = np.frombuffer(b"ACGTACGTACGTACGTACGT" + b"ACGTAC!TACGTACGTACGT", np.uint8).copy()
-    qual = np.frombuffer(b"I" * 40, np.uint8).copy()
-    ps = K.PairSet(seq, qual, np.array([0, 20], np.uint64), np.array([20, 20], np.uint16))
+    seq = np.frombuffer(b"ACGTACGTACGTACGTACGTACGTACGTAC" + b"ACGTAC!TACGTACGTACGTACGTACGTAC", np.uint8).copy()
+    qual = np.frombuffer(b"I" * 60, np.uint8).copy()
+    ps = K.PairSet(seq, qual, np.array([0, 30], np.uint64), np.array([30, 30], np.uint16))  # (>= min_kmer_len: not dropped)
     with pytest.raises(_lib.KcError) as ei:
         K.merge_pairs(ps)
     assert ei.value.code == _lib.KC_ERR_ARG

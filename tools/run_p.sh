@@ -1,0 +1,2 @@
+mkdir -p gpurun_out
+( timeout 120 python -m pytest tests/test_merge.py tests/test_zz_no_alloc.py -x -q -m gpu > gpurun_out/r02_merge_gpu2.log 2>&1; echo "merge+noalloc rc=$?"; tail -3 gpurun_out/r02_merge_gpu2.log )
