@@ -263,6 +263,18 @@ int kc_result_device_ptrs(kc_ctx *ctx, int extended, const uint64_t **keys, cons
 /* 64-bit order-independent checksum of the result (sum over entries of a mix of key words, count, L, R
  * and, when extended, the 8 ext counters); computed on the device. Same function in oracle/. */
 int kc_result_checksum(kc_ctx *ctx, int extended, uint64_t *checksum);
+/* The same checksum WITHOUT ANY ALLOCATION, for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it). No counterpart in the reference.
+ * The caller passes the result arrays as DEVICE pointers (e.g. from kc_result_device_ptrs; ext8 may be NULL) and the
+ * destination (host or device). Scratch is a file-scope device array of KC_NOALLOC_SCRATCH_WORDS x 8 bytes (32 KB) that every
+ * GPU which loads the library holds until exit; its address is looked up once per device (cudaGetSymbolAddress). The call makes
+ * no cudaMalloc / cudaFree / stream / event call, runs on the legacy default stream and is complete on return. More than
+ * KC_NOALLOC_MAX_ENTRIES entries: KC_ERR_ARG. ALL calls share the scratch array (every word a call reads it wrote itself, so
+ * earlier contents never leak into a result): calls that overlap on the GPU race -- serialise them. */
+#define KC_NOALLOC_SCRATCH_WORDS 4096
+#define KC_NOALLOC_MAX_ENTRIES (1ull << 31)
+int kc_checksum_noalloc(int device, const uint64_t *keys, const uint16_t *counts, const char *left, const char *right, const uint16_t *ext8,
+                        uint64_t n_entries, uint32_t n_words, uint64_t *checksum);
 /* Text dump, one "KMER count L R" line per survivor, sorted by key (kmer_dht.cpp:274-297 writes the same
  * lines unsorted and gzipped). extended adds the 8 counters. */
 int kc_dump_sorted(kc_ctx *ctx, const char *path, int extended);

@@ -97,6 +97,7 @@ PROTOTYPES = {
     "kc_dump_sorted": (C.c_int, [vp, C.c_char_p, C.c_int]),
     "kc_dump_kmers": (C.c_int, [vp, C.c_char_p, C.c_int]),
     "kc_lookup": (C.c_int, [vp, vp, C.c_uint64, vp, vp, vp]),
+    "kc_checksum_noalloc": (C.c_int, [C.c_int, vp, vp, vp, vp, vp, C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64)]),
     "kc_merge_pairs": (C.c_int, [C.c_int, vp, vp, vp, vp, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.POINTER(C.c_uint64), vp]),
     "kc_add_read_pairs": (C.c_int, [vp, vp, vp, vp, vp, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, vp]),
     "kc_owner_of": (C.c_int, [vp, vp]),
