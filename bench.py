@@ -766,6 +766,33 @@ def e2e_arm(K, env, args, spec, st0, reads, stats, occ_all, h2d_bytes, raw_local
     return out
 
 
+def merge_bench(K, env, n_pairs=2_000_000):
+    """Read-pair merging in front of the stage (kc_merge.cu replaces the pair loop of merge_reads(),
+    src/merge_reads.cpp:466-650): seeded synthetic pairs (C3's community, 150 bp mates, insert N(220, 40) so that most mates
+    overlap) as FASTQ characters in host memory -> kc_merge_pairs -> PackedRead bytes in host memory. Parity of this path:
+    tests/test_merge.py (reference goldens). Reported beside the headline, not part of it."""
+    import numpy as np
+
+    rs = K.generate("C3", 2 * n_pairs, n_genomes=20, insert_mean=220.0, insert_sd=40.0)
+    lut_b = np.frombuffer(b"ACGTNNNN", np.uint8)
+    seq = lut_b[rs.bytes & 7]
+    qual = (rs.bytes >> 3) + np.uint8(33)
+    ps = K.PairSet(seq, qual, rs.offsets, rs.lens)
+    best = None
+    for _ in range(3):
+        t0 = time.perf_counter()
+        reads, st = K.merge_pairs(ps, device=env.local_rank if hasattr(env, "local_rank") else 0)
+        wall = time.perf_counter() - t0
+        if best is None or st["ms_kernel"] < best[0]["ms_kernel"]:
+            best = (st, wall)
+    st, wall = best
+    ms = st["ms_kernel"]
+    return {"pairs": n_pairs, "merged": st["merged"], "ambiguous": st["ambiguous"], "kernel_ms": ms, "pairs_per_sec": n_pairs / (ms / 1e3),
+            "algorithmic_gbps": 3 * len(seq) / (ms / 1e3) / 1e9, "call_wall_ms": wall * 1e3, "gpu_launches": st["launches"],
+            "what": "2 bytes read + 1 written per base; kernel time by CUDA events inside kc_merge_pairs; the call's wall time includes its own "
+                    "cudaMalloc / H2D / D2H of pageable host arrays"}
+
+
 def sub_config_specs(args, world):
     """(label, spec overrides) of the other BASELINE configs this run can hold."""
     base = dict(m=0, filter=0, global_table=False, local_bins=0, record_bytes=0, table_slots=0)
@@ -816,6 +843,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--n-genomes", type=int, default=0, help="profiling only: fewer genomes keep the coverage of a smaller read set like the full workload's")
     ap.add_argument("--no-packed", action="store_true", help="skip the end-to-end pass that starts from the reference's PackedReads memory layout")
+    ap.add_argument("--no-merge", action="store_true", help="skip the read-pair merging measurement (kc_merge_pairs, beside the headline)")
     ap.add_argument("--no-lookup", action="store_true", help="skip the batched-lookup measurement against the finished result")
     ap.add_argument("--no-parity", action="store_true", help="skip the untimed parity pass against the CPU checker")
     ap.add_argument("--parity-reads", type=int, default=400_000, help="reads (all ranks together) of the parity pass")
@@ -873,6 +901,11 @@ def main():
             except Exception as e:  # noqa: BLE001 -- a sub-config must not take the headline down; the failure is reported
                 cfgs[label] = {"error": str(e)[:300]}
         line["configs"] = cfgs
+    if not args.no_merge and env.rank == 0:
+        try:
+            line["merge_pairs"] = merge_bench(K, env)
+        except Exception as e:  # noqa: BLE001 -- reported, not fatal: the step in front of the stage is not the headline
+            line["merge_pairs"] = {"error": str(e)[:300]}
     if env.rank == 0:
         print(json.dumps(line), flush=True)
     if env.dist is not None:
