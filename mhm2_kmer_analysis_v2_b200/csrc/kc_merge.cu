@@ -9,11 +9,12 @@
 //
 // One warp owns a pair (no CTA barrier):
 //   1. stage: mate 1 and its qualities, the reverse complement of mate 2 and its reversed qualities -> shared memory
-//   2. prefilter: lane l counts the character mismatches of offset g + l (32 offsets of the slide at a time; mate 1 is read
-//      at consecutive addresses across the lanes, mate 2 is a broadcast), giving up at the offset's mismatch budget
-//   3. the few offsets that pass (normally the true overlap alone) are scored by ONE lane in increasing order, exactly like the
-//      reference's inner loop -- its error-probability sum is a sum of doubles whose order must not change, and an N that
-//      meets a base zeroes a quality for all later offsets
+//   2. prefilter: lane l counts the character mismatches of offset g + l (32 offsets of the slide at a time), four characters
+//      per step (aligned 32-bit shared-memory loads, funnel shift, per-byte compare), giving up at the offset's mismatch budget
+//   3. the few offsets that pass (normally the true overlap alone) are scored in increasing order: the lanes classify 32
+//      positions at a time (two ballots), and only the EVENTS -- mismatches and N against N, a handful per overlap -- are walked
+//      in order with the reference's statements (kc_merge_core.cuh), so its error-probability sum (doubles, whose order must
+//      not change), its early exits and the qualities an N comparison zeroes for all later offsets come out identical
 //   4. merge: the lanes rewrite the overlap position by position and pack the result; an unmerged pair is packed as it came
 // Integer / byte work throughout; bound by the shared-memory pipe and the serial scoring, not by HBM (2 bytes read and 1
 // written per base).
@@ -52,7 +53,7 @@ struct MergeParams {
   MergeCounters *ctr;
 };
 
-__global__ void __launch_bounds__(MG_WARPS * 32) merge_kernel(MergeParams p) {
+__global__ void __launch_bounds__(MG_WARPS * 32, 4) merge_kernel(MergeParams p) {
   __shared__ uint8_t s_buf[MG_WARPS][4 * MG_MAXL];
   const uint32_t lane = lane_id();
   const int warp = threadIdx.x >> 5;
@@ -107,19 +108,35 @@ __global__ void __launch_bounds__(MG_WARPS * 32) merge_kernel(MergeParams p) {
         if (i < n_off) {
           int tm, em;
           merge_limits(len - i, tm, em);
-          pass = merge_prefilter(s1 + start_i + i, rc2, len - i, em);
+          pass = merge_prefilter(s1, start_i + i, rc2, len - i, em);
         }
         uint32_t m = __ballot_sync(0xffffffffu, pass);
         while (m && !stop) {
-          const int b = __ffs(m) - 1;
+          // score offset g + b: the lanes classify 32 positions at a time, then every lane walks the (few) events of the
+          // chunk in order -- the state is the same in all lanes, lane 0 stores the qualities an N comparison zeroes
+          const int oi = g + __ffs(m) - 1;
           m &= m - 1u;
-          if (lane == 0) merge_detailed(st, s1, q1, rc2, rq2, start_i, g + b, len, qo, c_q2p);
-          __syncwarp();
-          stop = __shfl_sync(0xffffffffu, st.stop, 0);
+          const int overlap = len - oi, p0 = start_i + oi;
+          int tm, em;
+          merge_limits(overlap, tm, em);
+          MergeEval ev;
+          merge_eval_init(ev);
+          for (int c = 0; c < overlap && !ev.broke; c += 32) {
+            const int j = c + (int)lane;
+            const bool valid = j < overlap;
+            const uint8_t ps = valid ? s1[p0 + j] : 0, rs = valid ? rc2[j] : 1;
+            const bool eq = valid && ps == rs;
+            const uint32_t eq_mask = __ballot_sync(0xffffffffu, eq);
+            const uint32_t ev_mask = __ballot_sync(0xffffffffu, valid && (!eq || ps == 'N'));
+            merge_chunk(st, ev, eq_mask, ev_mask, c, min(32, overlap - c), s1, q1, rc2, rq2, p0, em, qo, c_q2p, lane == 0);
+          }
+          merge_conclude(st, ev, oi, overlap);
+          __syncwarp();  // lane 0's quality stores are visible to the next offset's scoring
+          stop = st.stop;
         }
       }
-      best_i = __shfl_sync(0xffffffffu, st.best_i, 0);
-      const int aborted = __shfl_sync(0xffffffffu, st.abort_merge, 0);
+      best_i = st.best_i;  // (warp-uniform: every lane walked the same events)
+      const int aborted = st.abort_merge;
       if (lane == 0) {
         n_amb += st.ambiguous;
         bad_qual |= (unsigned)st.bad_qual;

@@ -73,11 +73,58 @@ KC_HD void merge_limits(int overlap, int &this_max_mismatch, int &error_max_mism
   error_max_mismatch = this_max_mismatch * 4 / 3 + 1;
 }
 
-// fast_count_mismatches(...) <= error_max_mismatch (src/merge_reads.cpp:186-247, 486): plain character inequality
-KC_HD bool merge_prefilter(const uint8_t *a, const uint8_t *b, int overlap, int error_max_mismatch) {
+// ---- small portable helpers (device intrinsics, plain C on the host) -----------------------------------------------------
+KC_HD uint32_t mc_load32(const uint8_t *p) {  // 4-byte aligned
+  return *reinterpret_cast<const uint32_t *>(p);
+}
+KC_HD uint32_t mc_funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) {  // low word of (hi:lo) >> sh, sh in {0, 8, 16, 24}
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_r(lo, hi, sh);
+#else
+  return sh ? (lo >> sh) | (hi << (32 - sh)) : lo;
+#endif
+}
+KC_HD uint32_t mc_ne_bytes(uint32_t a, uint32_t b) {  // 0xff in every byte where a and b differ
+#if defined(__CUDA_ARCH__)
+  return __vcmpne4(a, b);
+#else
+  uint32_t x = a ^ b, r = 0;
+  for (int k = 0; k < 4; k++)
+    if ((x >> (8 * k)) & 0xffu) r |= 0xffu << (8 * k);
+  return r;
+#endif
+}
+KC_HD int mc_popc(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __popc(x);
+#else
+  return __builtin_popcount(x);
+#endif
+}
+KC_HD int mc_ffs(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __ffs(x);
+#else
+  return __builtin_ffs((int)x);
+#endif
+}
+
+// fast_count_mismatches(...) <= error_max_mismatch (src/merge_reads.cpp:186-247, 486): plain character inequality, four
+// characters at a time. s1 and rc2 are 4-byte aligned buffers (readable up to the next multiple of 4 past their contents);
+// p0 = first character of mate 1 in the overlap (any alignment: two aligned words + a funnel shift).
+KC_HD bool merge_prefilter(const uint8_t *s1, int p0, const uint8_t *rc2, int overlap, int error_max_mismatch) {
+  const uint8_t *a_base = s1 + (p0 & ~3);
+  const uint32_t sh = (uint32_t)(p0 & 3) * 8u;
   int mm = 0;
-  for (int j = 0; j < overlap; j++) {
-    mm += a[j] != b[j];
+  uint32_t lo = mc_load32(a_base);
+  for (int w = 0; 4 * w < overlap; w++) {
+    const uint32_t hi = mc_load32(a_base + 4 * w + 4);
+    const uint32_t a = mc_funnel_r(lo, hi, sh), b = mc_load32(rc2 + 4 * w);
+    lo = hi;
+    uint32_t d = mc_ne_bytes(a, b);
+    const int rem = overlap - 4 * w;
+    if (rem < 4) d &= (1u << (8 * rem)) - 1u;
+    mm += mc_popc(d) >> 3;
     if (mm > error_max_mismatch) return false;
   }
   return true;
@@ -99,76 +146,106 @@ KC_HD void merge_scan_init(MergeScan &st) {
   st.bad_qual = 0;
 }
 
-// One offset i that passed the prefilter: src/merge_reads.cpp:488-578. s1 / q1 = mate 1 and its qualities, rc2 / rq2 = reverse
-// complement of mate 2 and its reversed qualities (working copies: an N that meets a base zeroes its quality for good).
-KC_HD void merge_detailed(MergeScan &st, const uint8_t *s1, uint8_t *q1, const uint8_t *rc2, uint8_t *rq2, int start_i, int i, int len,
-                          int qual_offset, const double *q2p) {
-  const int overlap = len - i;
-  int this_max_mismatch, error_max_mismatch;
-  merge_limits(overlap, this_max_mismatch, error_max_mismatch);
-  int matches = 0, mismatches = 0, bothNs = 0, Ncount = 0, overlapChecked = 0;
-  double perror = 0.0;
-  for (int j = 0; j < overlap; j++) {
-    overlapChecked++;
-    const int p = start_i + i + j;
-    const uint8_t ps = s1[p], rs = rc2[j];
-    if (ps == rs) {
-      matches++;
-      if (ps == 'N') {
-        Ncount += 2;
-        if (bothNs++) {
-          st.abort_merge++;
-          st.ambiguous++;
-          break;  // do not match multiple Ns in the same position -- 1 is okay
-        }
-      }
-    } else {
-      mismatches++;
-      if (ps == 'N') {
-        mismatches++;  // N still counts as a mismatch
-        Ncount++;
-        q1[p] = (uint8_t)qual_offset;
-        const int x = (int)rq2[j] - qual_offset;
-        if (x < 0 || x >= kQ2PerrorSize) {
-          st.bad_qual = 1;
-          st.stop = 1;
-          return;
-        }
-        perror += q2p[x];
-      } else if (rs == 'N') {
-        Ncount++;
-        mismatches++;
-        rq2[j] = (uint8_t)qual_offset;
-        const int x = (int)q1[p] - qual_offset;
-        if (x < 0 || x >= kQ2PerrorSize) {
-          st.bad_qual = 1;
-          st.stop = 1;
-          return;
-        }
-        perror += q2p[x];
-      }
-      const int a = (int)q1[p] - qual_offset, b = (int)rq2[j] - qual_offset;
-      if (a < 0 || b < 0 || a >= kQ2PerrorSize || b >= kQ2PerrorSize) {
-        st.bad_qual = 1;
-        st.stop = 1;
-        return;
-      }
-      const int diffq = a > b ? a - b : b - a;
-      if (diffq <= 2)
-        perror += 0.5;  // cap at flipping a coin when both quality scores are close
-      else
-        perror += q2p[diffq];
-    }
-    if (Ncount > 3) {
+// Scoring of one offset that passed the prefilter (src/merge_reads.cpp:488-545), restructured around EVENTS: a position where
+// the two calls agree on a base changes nothing but `matches` and `overlapChecked`, and neither of the loop's two exits can
+// fire there (their conditions were tested at the last event). So the positions are classified 32 at a time (in the kernel: one
+// per lane, two ballots), and only the events -- mismatches and N == N -- are walked in order with the reference's statements:
+// the counters, the error-probability sum (doubles, added in the reference's order) and the breaks come out identical.
+struct MergeEval {
+  int matches, mismatches, bothNs, Ncount, overlapChecked, broke;
+  double perror;
+};
+KC_HD void merge_eval_init(MergeEval &ev) {
+  ev.matches = ev.mismatches = ev.bothNs = ev.Ncount = ev.overlapChecked = ev.broke = 0;
+  ev.perror = 0.0;
+}
+
+// one event at overlap position j (p = its position in mate 1); returns true when the reference's loop breaks here.
+// `writer`: this caller stores the zeroed qualities (in the kernel every lane walks the events, lane 0 stores).
+KC_HD bool merge_event(MergeScan &st, MergeEval &ev, const uint8_t *s1, uint8_t *q1, const uint8_t *rc2, uint8_t *rq2, int p, int j,
+                       int error_max_mismatch, int qual_offset, const double *q2p, bool writer) {
+  const uint8_t ps = s1[p], rs = rc2[j];
+  if (ps == rs) {  // N == N (any other agreement is not an event)
+    ev.Ncount += 2;
+    if (ev.bothNs++) {
       st.abort_merge++;
       st.ambiguous++;
-      break;  // do not match reads with many Ns
+      return true;  // do not match multiple Ns in the same position -- 1 is okay
     }
-    if (mismatches > error_max_mismatch) break;
+  } else {
+    int qa = (int)q1[p], qb = (int)rq2[j];
+    ev.mismatches++;
+    if (ps == 'N') {
+      ev.mismatches++;  // N still counts as a mismatch
+      ev.Ncount++;
+      qa = qual_offset;
+      if (writer) q1[p] = (uint8_t)qual_offset;
+      const int x = qb - qual_offset;
+      if (x < 0 || x >= kQ2PerrorSize) {
+        st.bad_qual = 1;
+        st.stop = 1;
+        return true;
+      }
+      ev.perror += q2p[x];
+    } else if (rs == 'N') {
+      ev.Ncount++;
+      ev.mismatches++;
+      qb = qual_offset;
+      if (writer) rq2[j] = (uint8_t)qual_offset;
+      const int x = qa - qual_offset;
+      if (x < 0 || x >= kQ2PerrorSize) {
+        st.bad_qual = 1;
+        st.stop = 1;
+        return true;
+      }
+      ev.perror += q2p[x];
+    }
+    const int a = qa - qual_offset, b = qb - qual_offset;
+    if (a < 0 || b < 0 || a >= kQ2PerrorSize || b >= kQ2PerrorSize) {
+      st.bad_qual = 1;
+      st.stop = 1;
+      return true;
+    }
+    const int diffq = a > b ? a - b : b - a;
+    if (diffq <= 2)
+      ev.perror += 0.5;  // cap at flipping a coin when both quality scores are close
+    else
+      ev.perror += q2p[diffq];
   }
+  if (ev.Ncount > 3) {
+    st.abort_merge++;
+    st.ambiguous++;
+    return true;  // do not match reads with many Ns
+  }
+  return ev.mismatches > error_max_mismatch;
+}
+
+// 32 positions [c, c + n_valid) of the overlap: eq_mask = positions where the characters are equal, ev_mask = events
+KC_HD void merge_chunk(MergeScan &st, MergeEval &ev, uint32_t eq_mask, uint32_t ev_mask, int c, int n_valid, const uint8_t *s1, uint8_t *q1,
+                       const uint8_t *rc2, uint8_t *rq2, int p0, int error_max_mismatch, int qual_offset, const double *q2p, bool writer) {
+  while (ev_mask) {
+    const int b = mc_ffs(ev_mask) - 1;
+    ev_mask &= ev_mask - 1u;
+    if (merge_event(st, ev, s1, q1, rc2, rq2, p0 + c + b, c + b, error_max_mismatch, qual_offset, q2p, writer)) {
+      ev.matches += mc_popc(eq_mask & (0xffffffffu >> (31 - b)));
+      ev.overlapChecked = c + b + 1;
+      ev.broke = 1;
+      return;
+    }
+  }
+  ev.matches += mc_popc(eq_mask);
+  ev.overlapChecked = c + n_valid;
+}
+
+// verdict on offset i once its positions are scored: src/merge_reads.cpp:546-578
+KC_HD void merge_conclude(MergeScan &st, const MergeEval &ev, int i, int overlap) {
+  if (st.bad_qual) return;
+  int this_max_mismatch, error_max_mismatch;
+  merge_limits(overlap, this_max_mismatch, error_max_mismatch);
   int match_thres = overlap - this_max_mismatch;
   if (match_thres < kMergeMinOverlap) match_thres = kMergeMinOverlap;
-  if (matches >= match_thres && overlapChecked == overlap && mismatches <= this_max_mismatch && perror / overlap <= KC_MERGE_MAX_PERROR) {
+  if (ev.matches >= match_thres && ev.overlapChecked == overlap && ev.mismatches <= this_max_mismatch &&
+      ev.perror / overlap <= KC_MERGE_MAX_PERROR) {
     if (st.best_i < 0 && st.found_i < 0) {
       st.best_i = i;
     } else {
@@ -176,7 +253,7 @@ KC_HD void merge_detailed(MergeScan &st, const uint8_t *s1, uint8_t *q1, const u
       st.best_i = -1;
       st.stop = 1;
     }
-  } else if (overlapChecked == overlap && mismatches <= error_max_mismatch && perror / overlap <= KC_MERGE_MAX_PERROR * 4 / 3) {
+  } else if (ev.overlapChecked == overlap && ev.mismatches <= error_max_mismatch && ev.perror / overlap <= KC_MERGE_MAX_PERROR * 4 / 3) {
     st.found_i = i;  // lower threshold for detection of an ambiguous overlap
     if (st.best_i >= 0) {
       st.ambiguous++;  // ambiguous mapping found after a good one was

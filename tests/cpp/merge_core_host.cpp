@@ -43,8 +43,10 @@ int main(int argc, char **argv) {
       dropped++;
       continue;
     }
-    s1.assign(g1, g1 + len1), q1.assign(gq1, gq1 + len1);
-    rc2.resize(len2), rq2.resize(len2);
+    // (buffers padded to the next word + 4: the prefilter reads whole aligned words, as the kernel's shared-memory buffers allow)
+    s1.assign(len1 + 12, 0), q1.assign(len1 + 12, 0);
+    memcpy(s1.data(), g1, len1), memcpy(q1.data(), gq1, len1);
+    rc2.assign(len2 + 12, 0), rq2.assign(len2 + 12, 0);
     for (int t = 0; t < len2; t++) {
       rc2[t] = merge_comp_char(g2[len2 - 1 - t]);
       rq2[t] = gq2[len2 - 1 - t];
@@ -62,12 +64,26 @@ int main(int argc, char **argv) {
         if (i >= n_off) continue;
         int tm, em;
         merge_limits(len - i, tm, em);
-        if (merge_prefilter(s1.data() + start_i + i, rc2.data(), len - i, em)) m |= 1u << lane;
+        if (merge_prefilter(s1.data(), start_i + i, rc2.data(), len - i, em)) m |= 1u << lane;
       }
       while (m && !st.stop) {
-        const int b = __builtin_ffs(m) - 1;
+        const int oi = g + __builtin_ffs(m) - 1;
         m &= m - 1u;
-        merge_detailed(st, s1.data(), q1.data(), rc2.data(), rq2.data(), start_i, g + b, len, qo, q2p);
+        const int overlap = len - oi, p0 = start_i + oi;
+        int tm, em;
+        merge_limits(overlap, tm, em);
+        MergeEval ev;
+        merge_eval_init(ev);
+        for (int c = 0; c < overlap && !ev.broke; c += 32) {
+          unsigned eq_mask = 0, ev_mask = 0;  // the kernel's two ballots
+          for (int lane = 0; lane < 32 && c + lane < overlap; lane++) {
+            const uint8_t ps = s1[p0 + c + lane], rs = rc2[c + lane];
+            if (ps == rs) eq_mask |= 1u << lane;
+            if (ps != rs || ps == 'N') ev_mask |= 1u << lane;
+          }
+          merge_chunk(st, ev, eq_mask, ev_mask, c, overlap - c < 32 ? overlap - c : 32, s1.data(), q1.data(), rc2.data(), rq2.data(), p0, em, qo, q2p, true);
+        }
+        merge_conclude(st, ev, oi, overlap);
       }
     }
     if (st.bad_qual) return 4;
