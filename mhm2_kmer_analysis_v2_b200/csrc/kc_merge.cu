@@ -32,6 +32,7 @@ namespace kc {
 
 static const int MG_WARPS = 8;
 static const int MG_MAXL = KC_MERGE_MAX_READ_LEN;  // longest mate the kernel merges (shared memory per warp = 4 x this)
+static const int MG_CODEW = MG_MAXL / 8 + 2;       // code words per mate (+ the word the funnel shift reads past the end)
 
 __constant__ double c_q2p[kQ2PerrorSize] = KC_Q2PERROR_VALUES;
 
@@ -54,10 +55,12 @@ struct MergeParams {
 };
 
 __global__ void __launch_bounds__(MG_WARPS * 32, 4) merge_kernel(MergeParams p) {
-  __shared__ uint8_t s_buf[MG_WARPS][4 * MG_MAXL];
+  __shared__ __align__(16) uint8_t s_buf[MG_WARPS][4 * MG_MAXL];
+  __shared__ uint32_t s_code[MG_WARPS][2 * MG_CODEW];  // 4-bit character codes of mate 1 and of the reverse complement of mate 2
   const uint32_t lane = lane_id();
   const int warp = threadIdx.x >> 5;
   uint8_t *s1 = s_buf[warp], *q1 = s1 + MG_MAXL, *rc2 = q1 + MG_MAXL, *rq2 = rc2 + MG_MAXL;
+  uint32_t *s1c = s_code[warp], *rc2c = s1c + MG_CODEW;
   const int qo = p.qual_offset;
   unsigned long long n_merged = 0, n_amb = 0, sum_mlen = 0, sum_ovl = 0, max_len = 0, n_drop = 0, n_long = 0, sum_lens = 0;
   unsigned bad_char = 0, bad_qual = 0;
@@ -84,16 +87,35 @@ __global__ void __launch_bounds__(MG_WARPS * 32, 4) merge_kernel(MergeParams p) 
     const bool fits = len1 <= MG_MAXL && len2 <= MG_MAXL;
     if (fits) {
       // ---- 1. stage
-      for (int t = (int)lane; t < len1; t += 32) {
-        s1[t] = g1[t];
-        q1[t] = gq1[t];
+      // (five rounds of byte loads in flight per lane before the first store -- a 150-base mate in one trip: the mates come from DRAM)
+      for (int t0 = 0; t0 < len1 || t0 < len2; t0 += 160) {
+        uint8_t a[5], b[5], c[5], d[5];
+#pragma unroll
+        for (int u = 0; u < 5; u++) {
+          const int t = t0 + 32 * u + (int)lane;
+          a[u] = t < len1 ? g1[t] : 0;
+          b[u] = t < len1 ? gq1[t] : 0;
+          c[u] = t < len2 ? g2[len2 - 1 - t] : 'N';
+          d[u] = t < len2 ? gq2[len2 - 1 - t] : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < 5; u++) {
+          const int t = t0 + 32 * u + (int)lane;
+          if (t < len1) {
+            s1[t] = a[u];
+            q1[t] = b[u];
+          }
+          if (t < len2) {
+            const uint8_t cc = merge_comp_char(c[u]);
+            if (!cc) bad_char = 1;
+            rc2[t] = cc;
+            rq2[t] = d[u];
+          }
+        }
       }
-      for (int t = (int)lane; t < len2; t += 32) {
-        const uint8_t c = merge_comp_char(g2[len2 - 1 - t]);
-        if (!c) bad_char = 1;
-        rc2[t] = c;
-        rq2[t] = gq2[len2 - 1 - t];
-      }
+      __syncwarp();
+      for (int w = (int)lane; 8 * w < len1; w += 32) s1c[w] = merge_pack_codes(s1, w);
+      for (int w = (int)lane; 8 * w < len2; w += 32) rc2c[w] = merge_pack_codes(rc2, w);
       __syncwarp();
       // ---- 2 + 3. slide mate 2 along the tail of mate 1
       len = len2 < len1 ? len2 : len1;
@@ -108,7 +130,7 @@ __global__ void __launch_bounds__(MG_WARPS * 32, 4) merge_kernel(MergeParams p) 
         if (i < n_off) {
           int tm, em;
           merge_limits(len - i, tm, em);
-          pass = merge_prefilter(s1, start_i + i, rc2, len - i, em);
+          pass = merge_prefilter(s1c, start_i + i, rc2c, len - i, em);
         }
         uint32_t m = __ballot_sync(0xffffffffu, pass);
         while (m && !stop) {

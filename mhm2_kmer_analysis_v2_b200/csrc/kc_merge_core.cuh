@@ -77,7 +77,7 @@ KC_HD void merge_limits(int overlap, int &this_max_mismatch, int &error_max_mism
 KC_HD uint32_t mc_load32(const uint8_t *p) {  // 4-byte aligned
   return *reinterpret_cast<const uint32_t *>(p);
 }
-KC_HD uint32_t mc_funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) {  // low word of (hi:lo) >> sh, sh in {0, 8, 16, 24}
+KC_HD uint32_t mc_funnel_r(uint32_t lo, uint32_t hi, uint32_t sh) {  // low word of (hi:lo) >> sh, 0 <= sh < 32
 #if defined(__CUDA_ARCH__)
   return __funnelshift_r(lo, hi, sh);
 #else
@@ -109,22 +109,39 @@ KC_HD int mc_ffs(uint32_t x) {
 #endif
 }
 
-// fast_count_mismatches(...) <= error_max_mismatch (src/merge_reads.cpp:186-247, 486): plain character inequality, four
-// characters at a time. s1 and rc2 are 4-byte aligned buffers (readable up to the next multiple of 4 past their contents);
-// p0 = first character of mate 1 in the overlap (any alignment: two aligned words + a funnel shift).
-KC_HD bool merge_prefilter(const uint8_t *s1, int p0, const uint8_t *rc2, int overlap, int error_max_mismatch) {
-  const uint8_t *a_base = s1 + (p0 & ~3);
-  const uint32_t sh = (uint32_t)(p0 & 3) * 8u;
+// fast_count_mismatches(...) <= error_max_mismatch (src/merge_reads.cpp:186-247, 486) is plain character inequality. Here the
+// characters are first reduced to 4-bit codes, eight per 32-bit word (character 8 w + k in bits 4 k .. 4 k + 3 of word w):
+// A C G T N -> 0..4, anything else -> 5. The reverse complement of mate 2 only holds A C G T N (merge_comp_char), so two codes
+// are equal exactly when the two characters are (a lower-case or IUPAC character of mate 1 equals nothing, as in the reference).
+KC_HD uint32_t merge_char_code(uint8_t c) { return c == 'A' ? 0u : (c == 'C' ? 1u : (c == 'G' ? 2u : (c == 'T' ? 3u : (c == 'N' ? 4u : 5u)))); }
+// codes of characters [8 w, 8 w + 8) of a 4-byte aligned character buffer (readable to the next multiple of 8)
+KC_HD uint32_t merge_pack_codes(const uint8_t *chars, int w) {
+  const uint32_t lo = mc_load32(chars + 8 * w), hi = mc_load32(chars + 8 * w + 4);
+  uint32_t r = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int k = 0; k < 4; k++) {
+    r |= merge_char_code((uint8_t)(lo >> (8 * k))) << (4 * k);
+    r |= merge_char_code((uint8_t)(hi >> (8 * k))) << (4 * k + 16);
+  }
+  return r;
+}
+// mismatches of mate 1 from character p0 on against rc2 from character 0 on, `overlap` characters, eight per step; false as
+// soon as the budget is exceeded. s1c needs one readable word past the last one that holds a character of the overlap.
+KC_HD bool merge_prefilter(const uint32_t *s1c, int p0, const uint32_t *rc2c, int overlap, int error_max_mismatch) {
+  const uint32_t *a_base = s1c + (p0 >> 3);
+  const uint32_t sh = (uint32_t)(p0 & 7) * 4u;
   int mm = 0;
-  uint32_t lo = mc_load32(a_base);
-  for (int w = 0; 4 * w < overlap; w++) {
-    const uint32_t hi = mc_load32(a_base + 4 * w + 4);
-    const uint32_t a = mc_funnel_r(lo, hi, sh), b = mc_load32(rc2 + 4 * w);
+  uint32_t lo = a_base[0];
+  for (int w = 0; 8 * w < overlap; w++) {
+    const uint32_t hi = a_base[w + 1];
+    const uint32_t x = mc_funnel_r(lo, hi, sh) ^ rc2c[w];
     lo = hi;
-    uint32_t d = mc_ne_bytes(a, b);
-    const int rem = overlap - 4 * w;
-    if (rem < 4) d &= (1u << (8 * rem)) - 1u;
-    mm += mc_popc(d) >> 3;
+    uint32_t y = (x | (x >> 1) | (x >> 2)) & 0x11111111u;  // one bit per differing code (codes are < 8)
+    const int rem = overlap - 8 * w;
+    if (rem < 8) y &= (1u << (4 * rem)) - 1u;
+    mm += mc_popc(y);
     if (mm > error_max_mismatch) return false;
   }
   return true;

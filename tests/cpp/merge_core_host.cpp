@@ -52,6 +52,9 @@ int main(int argc, char **argv) {
       rq2[t] = gq2[len2 - 1 - t];
       if (!rc2[t]) return 3;
     }
+    std::vector<uint32_t> s1c(len1 / 8 + 3, 0xffffffffu), rc2c(len2 / 8 + 3, 0xffffffffu);  // (garbage past the end, as in the kernel)
+    for (int w = 0; 8 * w < len1; w++) s1c[w] = merge_pack_codes(s1.data(), w);
+    for (int w = 0; 8 * w < len2; w++) rc2c[w] = merge_pack_codes(rc2.data(), w);
     const int len = len2 < len1 ? len2 : len1;
     const int start_i = len == len1 ? 0 : len1 - len;
     const int n_off = len - kMergeMinOverlap + kMergeExtraTestOverlap;
@@ -64,7 +67,7 @@ int main(int argc, char **argv) {
         if (i >= n_off) continue;
         int tm, em;
         merge_limits(len - i, tm, em);
-        if (merge_prefilter(s1.data(), start_i + i, rc2.data(), len - i, em)) m |= 1u << lane;
+        if (merge_prefilter(s1c.data(), start_i + i, rc2c.data(), len - i, em)) m |= 1u << lane;
       }
       while (m && !st.stop) {
         const int oi = g + __builtin_ffs(m) - 1;
