@@ -61,6 +61,23 @@ __global__ void __launch_bounds__(MG_WARPS * 32, 4) merge_kernel(MergeParams p) 
   const int warp = threadIdx.x >> 5;
   uint8_t *s1 = s_buf[warp], *q1 = s1 + MG_MAXL, *rc2 = q1 + MG_MAXL, *rq2 = rc2 + MG_MAXL;
   uint32_t *s1c = s_code[warp], *rc2c = s1c + MG_CODEW;
+  // character tables, built once per CTA from the functions of kc_merge_core.cuh (the switches there diverge: a third of the
+  // kernel's instructions before this): complement (0 = illegal), PackedRead base code (0xff = illegal), 4-bit compare code
+  __shared__ uint8_t s_comp[256], s_base[256], s_ccode[256];
+  {
+    const uint8_t c = (uint8_t)threadIdx.x;
+    s_comp[c] = merge_comp_char(c);
+    const uint8_t v = merge_packed_byte(c, (uint8_t)p.qual_offset, p.qual_offset);
+    s_base[c] = v == 0xff ? 0xff : (uint8_t)(v & 7u);
+    s_ccode[c] = (uint8_t)merge_char_code(c);
+  }
+  __syncthreads();  // (the only CTA barrier; the warps are independent from here on)
+  auto packed = [&](uint8_t base, uint8_t qual) -> uint8_t {  // merge_packed_byte through the table
+    const uint8_t b = s_base[base];
+    int q = (int)qual - p.qual_offset;
+    q = q > 31 ? 31 : q;
+    return b == 0xff ? (uint8_t)0xff : (uint8_t)(b | ((uint8_t)q << 3));
+  };
   const int qo = p.qual_offset;
   unsigned long long n_merged = 0, n_amb = 0, sum_mlen = 0, sum_ovl = 0, max_len = 0, n_drop = 0, n_long = 0, sum_lens = 0;
   unsigned bad_char = 0, bad_qual = 0;
@@ -106,7 +123,7 @@ __global__ void __launch_bounds__(MG_WARPS * 32, 4) merge_kernel(MergeParams p) 
             q1[t] = b[u];
           }
           if (t < len2) {
-            const uint8_t cc = merge_comp_char(c[u]);
+            const uint8_t cc = s_comp[c[u]];
             if (!cc) bad_char = 1;
             rc2[t] = cc;
             rq2[t] = d[u];
@@ -114,8 +131,8 @@ __global__ void __launch_bounds__(MG_WARPS * 32, 4) merge_kernel(MergeParams p) 
         }
       }
       __syncwarp();
-      for (int w = (int)lane; 8 * w < len1; w += 32) s1c[w] = merge_pack_codes(s1, w);
-      for (int w = (int)lane; 8 * w < len2; w += 32) rc2c[w] = merge_pack_codes(rc2, w);
+      for (int w = (int)lane; 8 * w < len1; w += 32) s1c[w] = merge_pack_codes_lut(s1, w, s_ccode);
+      for (int w = (int)lane; 8 * w < len2; w += 32) rc2c[w] = merge_pack_codes_lut(rc2, w, s_ccode);
       __syncwarp();
       // ---- 2 + 3. slide mate 2 along the tail of mate 1
       len = len2 < len1 ? len2 : len1;
@@ -173,7 +190,7 @@ __global__ void __launch_bounds__(MG_WARPS * 32, 4) merge_kernel(MergeParams p) 
         for (int t = (int)lane; t < mlen; t += 32) {
           const uint8_t b = t < len1 ? s1[t] : rc2[overlap + t - len1];
           const uint8_t q = t < len1 ? q1[t] : rq2[overlap + t - len1];
-          const uint8_t v = merge_packed_byte(b, q, qo);
+          const uint8_t v = packed(b, q);
           if (v == 0xff) bad_char = 1;
           out[t] = v;
         }
@@ -195,12 +212,12 @@ __global__ void __launch_bounds__(MG_WARPS * 32, 4) merge_kernel(MergeParams p) 
     if (!merged) {
       // both mates as they came -- except that mate 1 keeps the qualities an N comparison zeroed (src/merge_reads.cpp:634)
       for (int t = (int)lane; t < len1; t += 32) {
-        const uint8_t v = merge_packed_byte(g1[t], fits ? q1[t] : gq1[t], qo);
+        const uint8_t v = packed(g1[t], fits ? q1[t] : gq1[t]);
         if (v == 0xff) bad_char = 1;
         out[t] = v;
       }
       for (int t = (int)lane; t < len2; t += 32) {
-        const uint8_t v = merge_packed_byte(g2[t], gq2[t], qo);
+        const uint8_t v = packed(g2[t], gq2[t]);
         if (v == 0xff) bad_char = 1;
         out[len1 + t] = v;
       }

@@ -127,6 +127,19 @@ KC_HD uint32_t merge_pack_codes(const uint8_t *chars, int w) {
   }
   return r;
 }
+// the same through a 256-entry table of merge_char_code (the kernel keeps one in shared memory: no branches, no divergence)
+KC_HD uint32_t merge_pack_codes_lut(const uint8_t *chars, int w, const uint8_t *code_lut) {
+  const uint32_t lo = mc_load32(chars + 8 * w), hi = mc_load32(chars + 8 * w + 4);
+  uint32_t r = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+  for (int k = 0; k < 4; k++) {
+    r |= (uint32_t)code_lut[(lo >> (8 * k)) & 0xffu] << (4 * k);
+    r |= (uint32_t)code_lut[(hi >> (8 * k)) & 0xffu] << (4 * k + 16);
+  }
+  return r;
+}
 // mismatches of mate 1 from character p0 on against rc2 from character 0 on, `overlap` characters, eight per step; false as
 // soon as the budget is exceeded. s1c needs one readable word past the last one that holds a character of the overlap.
 KC_HD bool merge_prefilter(const uint32_t *s1c, int p0, const uint32_t *rc2c, int overlap, int error_max_mismatch) {
