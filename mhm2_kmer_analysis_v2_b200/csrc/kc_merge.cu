@@ -31,6 +31,7 @@
 namespace kc {
 
 static const int MG_WARPS = 8;
+static_assert(MG_WARPS * 32 == 256, "merge_kernel fills its 256-entry character tables with one entry per thread");
 static const int MG_MAXL = KC_MERGE_MAX_READ_LEN;  // longest mate the kernel merges (shared memory per warp = 4 x this)
 static const int MG_CODEW = MG_MAXL / 8 + 2;       // code words per mate (+ the word the funnel shift reads past the end)
 
