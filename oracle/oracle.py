@@ -47,6 +47,8 @@ def lib():
         L.kco_result_size.restype = u64
         L.kco_result_size.argtypes = [vp, i32, i32]
         L.kco_result_copy.argtypes = [vp, i32, i32, vp, vp, vp, vp, vp]
+        L.kmo_merge_pairs.restype = i32
+        L.kmo_merge_pairs.argtypes = [vp, vp, vp, vp, u64, i32, i32, i32, vp, vp, vp, vp, vp]
         L.kco_result_checksum.restype = u64
         L.kco_result_checksum.argtypes = [vp, i32, i32]
         L.kco_avg_kmer_count.restype = C.c_double
@@ -232,3 +234,23 @@ def run_reference(reads_path, k, out_prefix=None, extended=False, ranks=1, dmin=
     if r.returncode != 0:
         raise RuntimeError(f"kcount_ref failed: {r.stderr[-2000:]}")
     return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def merge_pairs(seq, qual, offsets, lens, qual_offset=33, min_kmer_len=21, paired=True):
+    """oracle/merge_oracle.c (the reference's merge_reads pair loop, restated): FASTQ characters of the mates (reads 2 i, 2 i + 1
+    = pair i) -> (PackedRead bytes, offsets, lens of the reads the reference keeps, counters dict)."""
+    seq = np.ascontiguousarray(seq, np.uint8)
+    qual = np.ascontiguousarray(qual, np.uint8)
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    lens = np.ascontiguousarray(lens, np.uint16)
+    n = len(lens) // 2
+    ob = np.zeros(int(lens.astype(np.uint64).sum()) + 16, np.uint8)
+    oo = np.zeros(max(2 * n, 1), np.uint64)
+    ol = np.zeros(max(2 * n, 1), np.uint16)
+    n_out = np.zeros(1, np.uint64)
+    ctr = np.zeros(4, np.uint64)
+    rc = lib().kmo_merge_pairs(_p(seq), _p(qual), _p(offsets), _p(lens), n, qual_offset, min_kmer_len, int(paired), _p(ob), _p(oo), _p(ol), _p(n_out), _p(ctr))
+    if rc:
+        raise ValueError("merge oracle: a character the reference would DIE on")
+    k = int(n_out[0])
+    return ob, oo[:k].copy(), ol[:k].copy(), dict(merged=int(ctr[0]), ambiguous=int(ctr[1]), merged_len=int(ctr[2]), overlap_len=int(ctr[3]))

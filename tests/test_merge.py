@@ -66,6 +66,59 @@ def test_merge_arithmetic_on_host_equals_reference(name, host_tool, tmp_path):
     assert out.read_bytes() == expected(name)
 
 
+@pytest.mark.parametrize("name", NAMES)
+def test_merge_oracle_equals_reference(name):
+    """oracle/merge_oracle.c (plain-C restatement, the checker that travels) against the reference's own output."""
+    import oracle as O
+
+    e = INDEX[name]
+    p1, p2 = paths(name)
+    ps = K.PairSet.from_fastq(p1, p2, paired=e["paired"], qual_offset=e["qual_offset"])
+    ob, oo, ol, ctr = O.merge_pairs(ps.seq, ps.qual, ps.offsets, ps.lens, e["qual_offset"], e["min_kmer_len"], e["paired"])
+    assert as_text(K.ReadSet(ob, oo, ol), e["qual_offset"]) == expected(name)
+    assert ctr["merged"] == e["merged_or_dummy_mates"]
+
+
+def seeded_pairs(seed, n, **kw):
+    """mates from the generator of the golden fixtures (tests/golden/make_merge_golden.py) as a PairSet"""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("make_merge_golden", os.path.join(ROOT, "tests", "golden", "make_merge_golden.py"))
+    M = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(M)
+    seqs, quals = [], []
+    for s1, q1, s2, q2 in M.pairs(seed, n, **kw):
+        seqs += [s1, s2]
+        quals += [q1, q2]
+    lens = np.array([len(s) for s in seqs], np.uint16)
+    offs = np.concatenate([[0], np.cumsum(lens.astype(np.uint64))[:-1]]).astype(np.uint64)
+    return K.PairSet(np.frombuffer("".join(seqs).encode(), np.uint8).copy(), np.frombuffer("".join(quals).encode(), np.uint8).copy(), offs, lens)
+
+
+SEEDED = [dict(seed=101, n=3000), dict(seed=102, n=2000, lens=((20, 300), (20, 300)), insert=(180, 90), n_rate=0.01, err=0.02),
+          dict(seed=103, n=2000, period=11, err=0.005), dict(seed=104, n=1500, lens=((8, 60), (8, 60)), insert=(50, 20))]
+
+
+@pytest.mark.parametrize("cfg", SEEDED, ids=lambda c: f"seed{c['seed']}")
+def test_merge_host_arithmetic_equals_oracle_on_seeded_pairs(cfg, host_tool, tmp_path):
+    """the kernel's arithmetic (host run) against the oracle on fresh seeded pairs, beyond the committed goldens"""
+    import oracle as O
+
+    cfg = dict(cfg)
+    ps = seeded_pairs(cfg.pop("seed"), cfg.pop("n"), **cfg)
+    fq = tmp_path / "p.fq"
+    with open(fq, "w") as f:
+        for i in range(len(ps.lens)):
+            o, l = int(ps.offsets[i]), int(ps.lens[i])
+            f.write(f"@p{i // 2}/{i % 2 + 1}\n{bytes(ps.seq[o:o + l]).decode()}\n+\n{bytes(ps.qual[o:o + l]).decode()}\n")
+    out = tmp_path / "o.txt"
+    r = subprocess.run([host_tool, "33", "21", "1", str(out), str(fq)], check=True, stderr=subprocess.PIPE, text=True)
+    ob, oo, ol, ctr = O.merge_pairs(ps.seq, ps.qual, ps.offsets, ps.lens)
+    assert out.read_bytes() == as_text(K.ReadSet(ob, oo, ol), 33)
+    words = r.stderr.split()  # "pairs N merged N ambiguous N dropped N ..."
+    assert int(words[words.index("merged") + 1]) == ctr["merged"] and int(words[words.index("ambiguous") + 1]) == ctr["ambiguous"]
+
+
 def test_pair_reader_details(tmp_path):
     # unpaired file: every read gets the dummy mate N with quality = offset (src/merge_reads.cpp:352-371)
     p = tmp_path / "u.fq"
@@ -107,6 +160,20 @@ def test_merge_kernel_equals_reference(name):
     assert st["merged"] == e["merged_or_dummy_mates"]
     if st["dropped_short"] == 0 and st["pairs"]:
         assert st["sum_read_lens"] // (2 * st["pairs"]) == e["avg_read_len"]  # what merge_reads() returns
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cfg", SEEDED + [dict(seed=105, n=20000)], ids=lambda c: f"seed{c['seed']}")
+def test_merge_kernel_equals_oracle_on_seeded_pairs(cfg):
+    import oracle as O
+
+    cfg = dict(cfg)
+    ps = seeded_pairs(cfg.pop("seed"), cfg.pop("n"), **cfg)
+    reads, st = K.merge_pairs(ps)
+    ob, oo, ol, ctr = O.merge_pairs(ps.seq, ps.qual, ps.offsets, ps.lens)
+    assert np.array_equal(reads.lens, ol)
+    assert as_text(reads, 33) == as_text(K.ReadSet(ob, oo, ol), 33)
+    assert (st["merged"], st["ambiguous"], st["merged_len"], st["overlap_len"]) == (ctr["merged"], ctr["ambiguous"], ctr["merged_len"], ctr["overlap_len"])
 
 
 @pytest.mark.gpu
