@@ -2,7 +2,7 @@
  * (src/merge_reads.cpp:466-650) and of the PackedRead encoding of its output (src/packed_reads.cpp:99-126), one pair after the
  * other, position by position, in the reference's own order of statements. It is the checker that travels to the GPU box for
  * kc_merge.cu (tests/test_merge.py); nothing under mhm2_kmer_analysis_v2_b200/ includes, links or calls it.
- * Pinned: tests/test_merge.py holds it to tests/golden/merge/*, the outputs of the reference's own merge_reads.cpp
+ * Pinned: tests/test_merge.py holds it to the fixtures under tests/golden/merge, the outputs of the reference's own merge_reads.cpp
  * (oracle/_ref/merge_ref, made by tests/golden/make_merge_golden.py).
  * Deliberately written differently from the product (kc_merge_core.cuh works on 4-bit codes, ballots and events): this file
  * keeps strings and the reference's loop.
