@@ -177,12 +177,13 @@ def test_merge_kernel_equals_oracle_on_seeded_pairs(cfg):
 
 
 @pytest.mark.gpu
-def test_merged_pairs_feed_the_stage_without_leaving_hbm():
+@pytest.mark.parametrize("name", ["basic", "tiny"])  # tiny: dropped pairs stay behind as empty reads
+def test_merged_pairs_feed_the_stage_without_leaving_hbm(name):
     """kc_add_read_pairs -> kc_run equals kc_merge_pairs -> kc_add_reads -> kc_run (and so the oracle on the merged reads)."""
     import ctypes as C
 
-    e = INDEX["basic"]
-    ps = K.PairSet.from_fastq(paths("basic")[0])
+    e = INDEX[name]
+    ps = K.PairSet.from_fastq(paths(name)[0])
     reads, _ = K.merge_pairs(ps)
     a = K.KcountStage(k=21)
     a.add_reads(reads)
@@ -193,6 +194,7 @@ def test_merged_pairs_feed_the_stage_without_leaving_hbm():
     rc = b.L.kc_add_read_pairs(b.h, ps.seq.ctypes.data, ps.qual.ctypes.data, ps.offsets.ctypes.data, ps.lens.ctypes.data, len(ps), len(ps.seq),
                                33, e["min_kmer_len"], 1, C.byref(st))
     assert rc == 0 and st.merged == e["merged_or_dummy_mates"]
+    assert st.dropped_short == (2 * len(ps) - e["reads"]) // 2
     sb = b.run()
     assert b.checksum() == ca and sb["final_kmers"] == sa["final_kmers"] and sb["counted_kmers"] == sa["counted_kmers"]
     import oracle as O  # the checker (tests only)
