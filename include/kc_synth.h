@@ -70,7 +70,11 @@ void kc_read_set_free(kc_read_set *rs);
  * the dummy mate "N" (quality = offset) that the reference gives it. Names are normalised as FastqReader::get_fq_name does
  * (src/fastq.cpp:77-135: "/1" "/2", "-R1" "-R2", " 1:N:0:.." " 2:N:0:.."); a read 2 without its read 1 gets a faked "N" mate,
  * and -- as in the reference -- a read 1 without its read 2 gets one too and ENDS the file (src/merge_reads.cpp:446-461: the
- * end-of-file test looks at the already swapped-out name). Names that carry no pair marker are not supported. */
+ * end-of-file test looks at the already swapped-out name). Names that carry no pair marker are not supported.
+ * Plain (uncompressed) files of 4 MB or more are read by several threads (KC_HOST_THREADS, default = cores, at most 32): byte
+ * ranges are indexed in parallel, ONE thread runs the pairing logic over the record index, the characters are copied in
+ * parallel -- with exactly the streaming reader's result (anything unusual falls back to it; tests/test_merge.py holds the two
+ * to each other). 630 MB of FASTQ: 0.82 s streaming, 0.19 s with 8 threads. */
 typedef struct {
   char *seq, *qual;
   uint64_t n_bytes;

@@ -213,3 +213,93 @@ def test_merge_rejects_bad_characters():
     with pytest.raises(_lib.KcError) as ei:
         K.merge_pairs(ps)
     assert ei.value.code == _lib.KC_ERR_ARG
+
+
+def _read_both_ways(path_plain, path_gz, monkeypatch, paired=True, threads=5, chunk=64, path2=None):
+    """the same content through the parallel reader (plain file, cut into many small ranges) and the streaming reader (gzip)"""
+    def read(p, p2):
+        try:
+            ps = K.PairSet.from_fastq(p, p2, paired=paired)
+            return (0, bytes(ps.seq), bytes(ps.qual), list(ps.offsets), list(ps.lens), ps.missing_read1, ps.missing_read2)
+        except _lib.KcError as e:
+            return (e.code,)
+
+    monkeypatch.setenv("KC_HOST_THREADS", str(threads))
+    monkeypatch.setenv("KC_FASTQ_PAR_MIN_BYTES", "0")
+    monkeypatch.setenv("KC_FASTQ_PAR_MIN_CHUNK", str(chunk))
+    par = read(path_plain[0], path_plain[1] if path2 else None)
+    monkeypatch.setenv("KC_HOST_THREADS", "1")
+    monkeypatch.delenv("KC_FASTQ_PAR_MIN_BYTES")
+    stream = read(path_gz[0], path_gz[1] if path2 else None)
+    return par, stream
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_parallel_pair_reader_equals_streaming_reader_on_the_goldens(name, tmp_path, monkeypatch):
+    e = INDEX[name]
+    gz = paths(name)
+    plain = []
+    for i, g in enumerate(gz):
+        if g is None:
+            plain.append(None)
+            continue
+        p = tmp_path / f"f{i}.fq"
+        p.write_bytes(gzip.open(g, "rb").read())
+        plain.append(str(p))
+    monkeypatch.setenv("KC_FASTQ_PAR_STRICT", "1")  # well-formed files: the parallel path must be the one that answers
+    for threads, chunk in ((5, 64), (3, 1000), (8, 7)):
+        par, stream = _read_both_ways(plain, gz, monkeypatch, paired=e["paired"], threads=threads, chunk=chunk, path2=gz[1])
+        assert par == stream and par[0] == 0
+
+
+def test_parallel_pair_reader_equals_streaming_reader_on_awkward_files(tmp_path, monkeypatch):
+    """random files with missing mates, blank lines, CRLF, '@' / '+' at the start of quality lines, comments, no final newline,
+    and malformed records: same reads, same counters, same error code"""
+    import random
+
+    rng = random.Random(5)
+    taken = 0
+    for trial in range(60):
+        recs = []
+        n = rng.randint(0, 40)
+        for i in range(n):
+            L = rng.randint(0, 30)
+            s = "".join(rng.choice("ACGTN") for _ in range(L))
+            q1 = "".join(rng.choice("@+I5#!~") for _ in range(L))
+            q2 = "".join(rng.choice("@+I5#!~") for _ in range(L))
+            style = rng.choice(["/", "/", "/", " ", "-R"])
+            nm = lambda w: {"/": f"@r{i}/{w}", " ": f"@r{i} {w}:N:0:AC", "-R": f"@r{i}-R{w}"}[style] + rng.choice(["", "", " more", "\t x"])
+            mates = [(nm(1), s, q1), (nm(2), s[::-1], q2)]
+            drop = rng.random()
+            if drop < 0.08:
+                mates = mates[:1]
+            elif drop < 0.16:
+                mates = mates[1:]
+            recs += mates
+        eol = rng.choice(["\n", "\n", "\r\n"])
+        text = ""
+        for (h, s, q) in recs:
+            plus = rng.choice(["+", "+", "+" + h[1:]])
+            text += h + eol + s + rng.choice(["", "", " "]) + eol + plus + eol + q + eol
+            if rng.random() < 0.1:
+                text += eol
+        bad = rng.random()
+        if bad < 0.1 and recs:
+            text = text[: rng.randint(1, len(text))]  # cut anywhere
+        elif bad < 0.15:
+            text += "@x/1" + eol + "ACGT" + eol + "+" + eol + "III" + eol  # lengths differ
+        elif bad < 0.2 and text.endswith(eol):
+            text = text[: -len(eol)]  # no final newline
+        p = tmp_path / f"t{trial}.fq"
+        p.write_bytes(text.encode())
+        g = tmp_path / f"t{trial}.fq.gz"
+        with gzip.open(g, "wb") as f:
+            f.write(text.encode())
+        for paired in (True, False):
+            par, stream = _read_both_ways([str(p), None], [str(g), None], monkeypatch, paired=paired, threads=rng.randint(2, 9), chunk=rng.choice([1, 16, 100, 1000]))
+            assert par == stream, (trial, paired, text[:200])
+        monkeypatch.setenv("KC_FASTQ_PAR_STRICT", "1")
+        strict, _ = _read_both_ways([str(p), None], [str(g), None], monkeypatch, threads=4, chunk=16)
+        monkeypatch.delenv("KC_FASTQ_PAR_STRICT")
+        taken += strict[0] == 0
+    assert taken >= 30  # most of these files are well-formed enough for the parallel path (the rest fell back)
