@@ -766,6 +766,25 @@ def e2e_arm(K, env, args, spec, st0, reads, stats, occ_all, h2d_bytes, raw_local
     return out
 
 
+def merge_cpu_baseline(ps, st=None, sample_pairs=200_000):
+    """The same pair loop on one host core: oracle/merge_oracle.c (plain-C restatement of src/merge_reads.cpp:466-650; the
+    reference runs this loop on one rank per core) on a prefix of the pairs -- the cpu_baseline leg, the one place besides the
+    parity pass where bench.py may execute oracle/. Also a checker: its merged / ambiguous counts on the full set are not
+    compared here (tests/test_merge.py does that), only reported for the sample."""
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+
+    n = min(sample_pairs, len(ps))
+    end = int(ps.offsets[2 * n - 1]) + int(ps.lens[2 * n - 1]) if n else 0
+    t0 = time.perf_counter()
+    _, _, _, ctr = O.merge_pairs(ps.seq[:end], ps.qual[:end], ps.offsets[: 2 * n], ps.lens[: 2 * n])
+    dt = time.perf_counter() - t0
+    return {"value": n / dt if dt > 0 else None, "unit": "pairs/s", "cores": 1, "kind": "port", "sample": f"first {n} pairs, oracle/merge_oracle.c",
+            "merged_in_sample": ctr["merged"]}
+
+
 def merge_bench(K, env, n_pairs=2_000_000):
     """Read-pair merging in front of the stage (kc_merge.cu replaces the pair loop of merge_reads(),
     src/merge_reads.cpp:466-650): seeded synthetic pairs (C3's community, 150 bp mates, insert N(220, 40) so that most mates
@@ -787,7 +806,8 @@ def merge_bench(K, env, n_pairs=2_000_000):
             best = (st, wall)
     st, wall = best
     ms = st["ms_kernel"]
-    return {"pairs": n_pairs, "merged": st["merged"], "ambiguous": st["ambiguous"], "kernel_ms": ms, "pairs_per_sec": n_pairs / (ms / 1e3),
+    cpu = merge_cpu_baseline(ps, st)
+    return {"cpu_baseline": cpu, "pairs": n_pairs, "merged": st["merged"], "ambiguous": st["ambiguous"], "kernel_ms": ms, "pairs_per_sec": n_pairs / (ms / 1e3),
             "algorithmic_gbps": 3 * len(seq) / (ms / 1e3) / 1e9, "call_wall_ms": wall * 1e3, "gpu_launches": st["launches"],
             "what": "2 bytes read + 1 written per base; kernel time by CUDA events inside kc_merge_pairs; the call's wall time includes its own "
                     "cudaMalloc / H2D / D2H of pageable host arrays"}

@@ -4,8 +4,8 @@
 // PackedRead encoding of what it produces (src/packed_reads.cpp:99-126): mates come in as FASTQ text (sequence + quality
 // characters, as kc_fastq_read_pairs delivers them), the merged / unmerged reads come out in the one-byte-per-base PackedRead
 // encoding that kc_add_reads takes -- or go straight into a stage context without leaving HBM (kc_add_read_pairs).
-// Why on the GPU: the reference does this on the host cores, ~2 us per pair and core; for the 10 M pairs of one 20 M-read
-// GPU share that is ~1.3 s on 16 cores in front of a k-mer analysis that takes 0.075 s.
+// Why on the GPU: the reference does this on the host cores, ~14 us per pair and core (measured: oracle/_ref/merge_ref, 200 K pairs
+// in 2.9 s); for the 10 M pairs of one 20 M-read GPU share that is ~9 s on 16 cores in front of a k-mer analysis that takes 0.075 s.
 //
 // One warp owns a pair (no CTA barrier):
 //   1. stage: mate 1 and its qualities, the reverse complement of mate 2 and its reversed qualities -> shared memory
